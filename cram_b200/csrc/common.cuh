@@ -1,0 +1,98 @@
+// Shared helpers for libcram_b200 (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+
+#include "../../include/cram_b200.h"
+
+namespace cram {
+
+void set_error(const char* fmt, ...);
+
+#define CRAM_REQUIRE(cond, ...)          \
+  do {                                   \
+    if (!(cond)) {                       \
+      ::cram::set_error(__VA_ARGS__);    \
+      return CRAM_ERR_INVALID;           \
+    }                                    \
+  } while (0)
+
+#define CRAM_CUDA(expr)                                                                       \
+  do {                                                                                        \
+    cudaError_t _e = (expr);                                                                  \
+    if (_e != cudaSuccess) {                                                                  \
+      ::cram::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return CRAM_ERR_CUDA;                                                                   \
+    }                                                                                         \
+  } while (0)
+
+inline int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("launch of %s failed: %s", what, cudaGetErrorString(e));
+    return CRAM_ERR_CUDA;
+  }
+  return CRAM_OK;
+}
+
+// B200: 148 SMs. Queried once per process; used to size persistent grids.
+int sm_count();
+
+template <typename T>
+struct DType;
+template <>
+struct DType<float> {
+  static constexpr int code = CRAM_F32;
+  __device__ static float to_f(float x) { return x; }
+  __device__ static float from_f(float x) { return x; }
+};
+template <>
+struct DType<__half> {
+  static constexpr int code = CRAM_F16;
+  __device__ static float to_f(__half x) { return __half2float(x); }
+  __device__ static __half from_f(float x) { return __float2half_rn(x); }
+};
+template <>
+struct DType<__nv_bfloat16> {
+  static constexpr int code = CRAM_BF16;
+  __device__ static float to_f(__nv_bfloat16 x) { return __bfloat162float(x); }
+  __device__ static __nv_bfloat16 from_f(float x) { return __float2bfloat16_rn(x); }
+};
+
+// round a float through the model dtype (what a torch op on that dtype stores)
+template <typename T>
+__device__ __forceinline__ float round_to(float x) {
+  return DType<T>::to_f(DType<T>::from_f(x));
+}
+
+// load a log-credibility value of runtime dtype as float
+__device__ __forceinline__ float load_logcred(const void* p, int64_t i, int dtype) {
+  if (dtype == CRAM_BF16) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[i]);
+  if (dtype == CRAM_F16) return __half2float(reinterpret_cast<const __half*>(p)[i]);
+  return reinterpret_cast<const float*>(p)[i];
+}
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ int warp_max_i(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+inline size_t dtype_size(int dtype) { return dtype == CRAM_F32 ? 4 : 2; }
+
+}  // namespace cram

@@ -1,0 +1,335 @@
+// HBM-bound layer glue around the library GEMMs, plus the sweep's splice / answer-logit kernels and
+// the paged-KV append. Every kernel rounds where HF's eager modules round (transformers
+// models/llama/modeling_llama.py:52-70, 138-176, 178-186) so that the host forward tracks the hooked
+// reference within bf16 noise. All are streaming kernels: 16-byte accesses, one pass where possible.
+#include "common.cuh"
+
+namespace cram {
+
+template <typename T>
+struct Vec {  // 16 bytes of T
+  static constexpr int N = 16 / sizeof(T);
+  T v[N];
+};
+template <typename T>
+__device__ __forceinline__ Vec<T> ldvec(const T* p) {
+  Vec<T> r;
+  *reinterpret_cast<uint4*>(&r) = *reinterpret_cast<const uint4*>(p);
+  return r;
+}
+template <typename T>
+__device__ __forceinline__ void stvec(T* p, const Vec<T>& r) {
+  *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(&r);
+}
+
+// ------------------------------------------------------------------------------------------------
+// RMSNorm (+ fused residual add). One CTA per row.
+// ------------------------------------------------------------------------------------------------
+constexpr int kNormThreads = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(kNormThreads)
+rmsnorm_kernel(T* __restrict__ x, const T* __restrict__ residual, const T* __restrict__ w, T* __restrict__ out,
+               int hidden, float eps) {
+  constexpr int N = Vec<T>::N;
+  __shared__ float s_part[kNormThreads / 32];
+  __shared__ float s_inv;
+  T* xr = x + (int64_t)blockIdx.x * hidden;
+  const T* rr = residual ? residual + (int64_t)blockIdx.x * hidden : nullptr;
+  T* orow = out + (int64_t)blockIdx.x * hidden;
+  float ss = 0.f;
+  for (int i = threadIdx.x * N; i < hidden; i += kNormThreads * N) {
+    Vec<T> a = ldvec(xr + i);
+    if (rr) {
+      Vec<T> b = ldvec(rr + i);
+#pragma unroll
+      for (int j = 0; j < N; ++j) a.v[j] = DType<T>::from_f(DType<T>::to_f(b.v[j]) + DType<T>::to_f(a.v[j]));
+      stvec(xr + i, a);
+    }
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+      float f = DType<T>::to_f(a.v[j]);
+      ss += f * f;
+    }
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < kNormThreads / 32 ? s_part[threadIdx.x] : 0.f;
+    v = warp_sum(v);
+    if (threadIdx.x == 0) s_inv = rsqrtf(v / (float)hidden + eps);
+  }
+  __syncthreads();
+  const float inv = s_inv;
+  for (int i = threadIdx.x * N; i < hidden; i += kNormThreads * N) {
+    Vec<T> a = ldvec(xr + i);  // same thread wrote these elements above; L1-resident
+    Vec<T> ww = ldvec(w + i);
+    Vec<T> o;
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+      float n = round_to<T>(DType<T>::to_f(a.v[j]) * inv);
+      o.v[j] = DType<T>::from_f(DType<T>::to_f(ww.v[j]) * n);
+    }
+    stvec(orow + i, o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Rotary embedding in place on the first n_rot_heads heads of each row (Q heads then K heads of a
+// fused QKV buffer). out = x*cos + rotate_half(x)*sin with HF's three roundings.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void rope_kernel(T* __restrict__ qk, int64_t row_stride, int64_t n_rows, int n_rot_heads, int head_dim,
+                            const T* __restrict__ cos_t, const T* __restrict__ sin_t,
+                            const int32_t* __restrict__ positions) {
+  constexpr int N = Vec<T>::N;
+  const int half = head_dim / 2;
+  const int vec_per_head = half / N;
+  const int64_t per_row = (int64_t)n_rot_heads * vec_per_head;
+  const int64_t total = n_rows * per_row;
+  for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = idx / per_row;
+    const int rem = (int)(idx - r * per_row);
+    const int h = rem / vec_per_head;
+    const int j = (rem - h * vec_per_head) * N;
+    const int pos = positions[r];
+    T* base = qk + r * row_stride + (int64_t)h * head_dim;
+    Vec<T> x1 = ldvec(base + j), x2 = ldvec(base + j + half);
+    Vec<T> c1 = ldvec(cos_t + (int64_t)pos * head_dim + j), c2 = ldvec(cos_t + (int64_t)pos * head_dim + j + half);
+    Vec<T> s1 = ldvec(sin_t + (int64_t)pos * head_dim + j), s2 = ldvec(sin_t + (int64_t)pos * head_dim + j + half);
+    Vec<T> o1, o2;
+#pragma unroll
+    for (int e = 0; e < N; ++e) {
+      const float a = DType<T>::to_f(x1.v[e]), b = DType<T>::to_f(x2.v[e]);
+      o1.v[e] = DType<T>::from_f(round_to<T>(a * DType<T>::to_f(c1.v[e])) + round_to<T>(-b * DType<T>::to_f(s1.v[e])));
+      o2.v[e] = DType<T>::from_f(round_to<T>(b * DType<T>::to_f(c2.v[e])) + round_to<T>(a * DType<T>::to_f(s2.v[e])));
+    }
+    stvec(base + j, o1);
+    stvec(base + j + half, o2);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// SwiGLU gate: out = dtype(dtype(silu(gate)) * up), gate/up the two halves of a fused projection row.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void silu_mul_kernel(const T* __restrict__ gu, T* __restrict__ out, int64_t n_rows, int inter) {
+  constexpr int N = Vec<T>::N;
+  const int vec_per_row = inter / N;
+  const int64_t total = n_rows * vec_per_row;
+  for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = idx / vec_per_row;
+    const int j = (int)(idx - r * vec_per_row) * N;
+    Vec<T> g = ldvec(gu + r * 2 * inter + j), u = ldvec(gu + r * 2 * inter + inter + j), o;
+#pragma unroll
+    for (int e = 0; e < N; ++e) {
+      const float x = DType<T>::to_f(g.v[e]);
+      const float s = round_to<T>(x / (1.0f + expf(-x)));
+      o.v[e] = DType<T>::from_f(s * DType<T>::to_f(u.v[e]));
+    }
+    stvec(out + r * inter + j, o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Sweep: build n_var single-head variants of an attention output.
+// ------------------------------------------------------------------------------------------------
+__global__ void splice_heads_kernel(const uint4* __restrict__ clean, const uint4* __restrict__ biased,
+                                    const int32_t* __restrict__ heads, int n_var, int64_t n_rows, int vec_per_row,
+                                    int vec_per_head, uint4* __restrict__ out) {
+  const int64_t per_var = n_rows * vec_per_row;
+  const int64_t total = per_var * n_var;
+  for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int v = (int)(idx / per_var);
+    const int64_t within = idx - (int64_t)v * per_var;
+    const int col = (int)(within % vec_per_row);
+    const bool take = (col / vec_per_head) == heads[v];
+    out[idx] = take ? biased[within] : clean[within];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Sweep epilogue: final norm + lm_head rows of the answer tokens + sum + IE, one CTA per variant.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+answer_ie_kernel(const T* __restrict__ x, int64_t T_len, int hidden, const T* __restrict__ norm_w, float eps,
+                 const T* __restrict__ lm_head, const int64_t* __restrict__ answer_ids, int n_answer,
+                 const float* __restrict__ ori, float* __restrict__ cur, float* __restrict__ ie) {
+  __shared__ float s_part[8];
+  __shared__ float s_bcast;
+  const int v = blockIdx.x;
+  float acc_sum = 0.f;  // thread 0 only
+  for (int k = 0; k < n_answer; ++k) {
+    const T* row = x + ((int64_t)v * T_len + (T_len - n_answer + k)) * hidden;
+    const T* wrow = lm_head + answer_ids[k] * (int64_t)hidden;
+    float ss = 0.f;
+    for (int i = threadIdx.x; i < hidden; i += 256) {
+      const float f = DType<T>::to_f(row[i]);
+      ss += f * f;
+    }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      float t = threadIdx.x < 8 ? s_part[threadIdx.x] : 0.f;
+      t = warp_sum(t);
+      if (threadIdx.x == 0) s_bcast = rsqrtf(t / (float)hidden + eps);
+    }
+    __syncthreads();
+    const float inv = s_bcast;
+    float dot = 0.f;
+    for (int i = threadIdx.x; i < hidden; i += 256) {
+      const float n = round_to<T>(DType<T>::to_f(row[i]) * inv);
+      const float h = round_to<T>(DType<T>::to_f(norm_w[i]) * n);
+      dot += h * DType<T>::to_f(wrow[i]);
+    }
+    dot = warp_sum(dot);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = dot;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = 0.f;
+      for (int i = 0; i < 8; ++i) t += s_part[i];
+      acc_sum += round_to<T>(t);  // one logit, stored in model dtype
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const float c = round_to<T>(acc_sum);  // .sum() of a model-dtype tensor: fp32 accumulate, one rounding
+    if (cur) cur[v] = c;
+    if (ie && ori) ie[v] = round_to<T>(ori[0] - c);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Paged KV append.
+// ------------------------------------------------------------------------------------------------
+__global__ void kv_append_kernel(const uint4* __restrict__ k, const uint4* __restrict__ v, int64_t k_stride_v,
+                                 int64_t v_stride_v, int64_t n_rows, int vec_per_row,
+                                 const int64_t* __restrict__ slot_mapping, uint4* __restrict__ kc,
+                                 uint4* __restrict__ vc, int64_t page_stride_v, int64_t token_stride_v, int page_size) {
+  const int64_t total = n_rows * vec_per_row;
+  for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = idx / vec_per_row;
+    const int c = (int)(idx - r * vec_per_row);
+    const int64_t slot = slot_mapping[r];
+    if (slot < 0) continue;
+    const int64_t dst = (slot / page_size) * page_stride_v + (slot % page_size) * token_stride_v + c;
+    kc[dst] = k[r * k_stride_v + c];
+    vc[dst] = v[r * v_stride_v + c];
+  }
+}
+
+static inline int stream_grid(int64_t work_items, int threads) {
+  int64_t b = (work_items + threads - 1) / threads;
+  int64_t cap = (int64_t)sm_count() * 16;  // multiple of the SM count; grid-stride covers the rest
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+}  // namespace cram
+
+using namespace cram;
+
+#define DISPATCH_DTYPE(dtype, ...)                          \
+  switch (dtype) {                                          \
+    case CRAM_F32: { using T = float; __VA_ARGS__; break; } \
+    case CRAM_F16: { using T = __half; __VA_ARGS__; break; } \
+    case CRAM_BF16: { using T = __nv_bfloat16; __VA_ARGS__; break; } \
+    default: set_error("bad dtype %d", dtype); return CRAM_ERR_INVALID; \
+  }
+
+extern "C" int cram_rmsnorm(void* x, const void* residual, const void* weight, void* out, int64_t n_rows, int hidden,
+                            float eps, int dtype, cram_stream_t stream) {
+  CRAM_REQUIRE(n_rows >= 0 && hidden > 0, "cram_rmsnorm: bad shape");
+  if (n_rows == 0) return CRAM_OK;
+  const int vec = 16 / (int)dtype_size(dtype);
+  CRAM_REQUIRE(hidden % vec == 0, "cram_rmsnorm: hidden %d not a multiple of %d", hidden, vec);
+  CRAM_REQUIRE(aligned16(x) && aligned16(weight) && aligned16(out) && (!residual || aligned16(residual)),
+               "cram_rmsnorm: pointers must be 16-byte aligned");
+  CRAM_REQUIRE(n_rows < (1ll << 31), "cram_rmsnorm: too many rows");
+  DISPATCH_DTYPE(dtype, (rmsnorm_kernel<T><<<(unsigned)n_rows, kNormThreads, 0, (cudaStream_t)stream>>>(
+                            (T*)x, (const T*)residual, (const T*)weight, (T*)out, hidden, eps)));
+  return check_launch("rmsnorm_kernel");
+}
+
+extern "C" int cram_rope(void* qk, int64_t row_stride, int64_t n_rows, int n_rot_heads, int head_dim,
+                         const void* cos_table, const void* sin_table, const int32_t* positions, int dtype,
+                         cram_stream_t stream) {
+  CRAM_REQUIRE(n_rows >= 0 && n_rot_heads > 0 && head_dim > 0, "cram_rope: bad shape");
+  if (n_rows == 0) return CRAM_OK;
+  const int vec = 16 / (int)dtype_size(dtype);
+  CRAM_REQUIRE((head_dim / 2) % vec == 0 && row_stride % vec == 0, "cram_rope: head_dim/2 and row_stride must be multiples of %d", vec);
+  CRAM_REQUIRE(aligned16(qk) && aligned16(cos_table) && aligned16(sin_table), "cram_rope: pointers must be 16-byte aligned");
+  const int64_t items = n_rows * n_rot_heads * (head_dim / 2 / vec);
+  DISPATCH_DTYPE(dtype, (rope_kernel<T><<<stream_grid(items, 256), 256, 0, (cudaStream_t)stream>>>(
+                            (T*)qk, row_stride, n_rows, n_rot_heads, head_dim, (const T*)cos_table,
+                            (const T*)sin_table, positions)));
+  return check_launch("rope_kernel");
+}
+
+extern "C" int cram_silu_mul(const void* gate_up, void* out, int64_t n_rows, int inter, int dtype,
+                             cram_stream_t stream) {
+  CRAM_REQUIRE(n_rows >= 0 && inter > 0, "cram_silu_mul: bad shape");
+  if (n_rows == 0) return CRAM_OK;
+  const int vec = 16 / (int)dtype_size(dtype);
+  CRAM_REQUIRE(inter % vec == 0, "cram_silu_mul: inter must be a multiple of %d", vec);
+  CRAM_REQUIRE(aligned16(gate_up) && aligned16(out), "cram_silu_mul: pointers must be 16-byte aligned");
+  const int64_t items = n_rows * (inter / vec);
+  DISPATCH_DTYPE(dtype, (silu_mul_kernel<T><<<stream_grid(items, 256), 256, 0, (cudaStream_t)stream>>>(
+                            (const T*)gate_up, (T*)out, n_rows, inter)));
+  return check_launch("silu_mul_kernel");
+}
+
+extern "C" int cram_sweep_splice_heads(const void* clean, const void* biased, const int32_t* heads, int n_var,
+                                       int64_t n_rows, int n_heads, int head_dim, int dtype, void* out,
+                                       cram_stream_t stream) {
+  CRAM_REQUIRE(n_var >= 0 && n_rows >= 0 && n_heads > 0 && head_dim > 0, "cram_sweep_splice_heads: bad shape");
+  if (n_var == 0 || n_rows == 0) return CRAM_OK;
+  const int vec = 16 / (int)dtype_size(dtype);
+  CRAM_REQUIRE(head_dim % vec == 0, "cram_sweep_splice_heads: head_dim must be a multiple of %d", vec);
+  CRAM_REQUIRE(aligned16(clean) && aligned16(biased) && aligned16(out), "cram_sweep_splice_heads: 16-byte alignment");
+  const int vec_per_head = head_dim / vec, vec_per_row = n_heads * vec_per_head;
+  const int64_t items = (int64_t)n_var * n_rows * vec_per_row;
+  splice_heads_kernel<<<stream_grid(items, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const uint4*)clean, (const uint4*)biased, heads, n_var, n_rows, vec_per_row, vec_per_head, (uint4*)out);
+  return check_launch("splice_heads_kernel");
+}
+
+extern "C" int cram_sweep_answer_ie(const void* x, int n_var, int64_t seq_len, int hidden, const void* norm_weight,
+                                    float rms_eps, const void* lm_head, const int64_t* answer_ids, int n_answer,
+                                    int dtype, const float* ori, float* cur, float* ie, cram_stream_t stream) {
+  CRAM_REQUIRE(n_var >= 0 && hidden > 0 && n_answer > 0 && n_answer <= seq_len, "cram_sweep_answer_ie: bad shape");
+  if (n_var == 0) return CRAM_OK;
+  DISPATCH_DTYPE(dtype, (answer_ie_kernel<T><<<n_var, 256, 0, (cudaStream_t)stream>>>(
+                            (const T*)x, seq_len, hidden, (const T*)norm_weight, rms_eps, (const T*)lm_head, answer_ids,
+                            n_answer, ori, cur, ie)));
+  return check_launch("answer_ie_kernel");
+}
+
+extern "C" int cram_kv_append(const void* k, const void* v, int64_t k_row_stride, int64_t v_row_stride, int64_t n_rows,
+                              int n_kv_heads, int head_dim, int dtype, const int64_t* slot_mapping, void* k_cache,
+                              void* v_cache, int64_t page_stride, int64_t token_stride, int page_size,
+                              cram_stream_t stream) {
+  CRAM_REQUIRE(n_rows >= 0 && n_kv_heads > 0 && head_dim > 0 && page_size > 0, "cram_kv_append: bad shape");
+  if (n_rows == 0) return CRAM_OK;
+  const int vec = 16 / (int)dtype_size(dtype);
+  CRAM_REQUIRE((n_kv_heads * head_dim) % vec == 0 && k_row_stride % vec == 0 && v_row_stride % vec == 0 &&
+                   page_stride % vec == 0 && token_stride % vec == 0,
+               "cram_kv_append: strides must be multiples of %d elements", vec);
+  CRAM_REQUIRE(aligned16(k) && aligned16(v) && aligned16(k_cache) && aligned16(v_cache), "cram_kv_append: 16-byte alignment");
+  const int vec_per_row = n_kv_heads * head_dim / vec;
+  kv_append_kernel<<<stream_grid(n_rows * vec_per_row, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const uint4*)k, (const uint4*)v, k_row_stride / vec, v_row_stride / vec, n_rows, vec_per_row, slot_mapping,
+      (uint4*)k_cache, (uint4*)v_cache, page_stride / vec, token_stride / vec, page_size);
+  return check_launch("kv_append_kernel");
+}

@@ -1,0 +1,314 @@
+"""Host-side forward of a Llama / Qwen2 decoder on packed variable-length rows.
+
+This is the runtime that carries the credibility path on a B200: the dense projections are library
+GEMMs (torch -> cuBLASLt), everything between them is libcram_b200.so -- fused RMSNorm(+residual),
+rotary, SwiGLU gate, the tcgen05 credibility-biased attention, paged-KV append and the decode
+attention. It replaces, for the hooked layers, HF's self_attn forward under the reference's
+forward_pre_hook (utils/re_weighting.py:120-124): the hook's dense mask becomes a per-key
+log-credibility vector plus a per-layer head bitmask.
+
+Rows of all sequences are packed ([sum(T_i), hidden]); ``cu_seqlens`` delimits them.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.nn.functional as F
+
+from . import ops
+
+
+@dataclass
+class ModelSpec:
+    num_layers: int
+    num_heads: int
+    num_kv_heads: int
+    head_dim: int
+    hidden: int
+    intermediate: int
+    vocab: int
+    rms_eps: float = 1e-6
+    rope_theta: float = 10000.0
+    qkv_bias: bool = False
+    tie_embeddings: bool = False
+
+    @classmethod
+    def from_hf(cls, cfg) -> "ModelSpec":
+        hd = getattr(cfg, "head_dim", None) or cfg.hidden_size // cfg.num_attention_heads
+        rp = getattr(cfg, "rope_parameters", None)
+        theta = rp.get("rope_theta") if isinstance(rp, dict) and rp.get("rope_theta") else getattr(cfg, "rope_theta", 10000.0)
+        return cls(cfg.num_hidden_layers, cfg.num_attention_heads, cfg.num_key_value_heads, hd, cfg.hidden_size,
+                   cfg.intermediate_size, cfg.vocab_size, cfg.rms_norm_eps, float(theta),
+                   qkv_bias=(cfg.model_type == "qwen2") or bool(getattr(cfg, "attention_bias", False)),
+                   tie_embeddings=bool(getattr(cfg, "tie_word_embeddings", False)))
+
+
+LLAMA3_8B = ModelSpec(32, 32, 8, 128, 4096, 14336, 128256, 1e-5, 500000.0)
+QWEN2_7B = ModelSpec(28, 28, 4, 128, 3584, 18944, 152064, 1e-6, 1000000.0, qkv_bias=True)
+LLAMA3_70B = ModelSpec(80, 64, 8, 128, 8192, 28672, 128256, 1e-5, 500000.0)
+TINY = ModelSpec(2, 4, 2, 64, 256, 512, 1000, 1e-5, 10000.0)
+
+
+@dataclass
+class SweepCapture:
+    """Per-layer tensors of one clean forward that the IE sweep re-uses (kernel 3)."""
+    x_in: List[torch.Tensor] = field(default_factory=list)   # residual stream entering the layer (after the fused add)
+    qkv: List[torch.Tensor] = field(default_factory=list)    # fused projections, rotary applied
+    attn: List[torch.Tensor] = field(default_factory=list)   # clean attention output
+
+
+class PagedKV:
+    """Paged KV cache: per layer K and V of shape [n_pages, page_size, n_kv_heads, head_dim]."""
+
+    def __init__(self, spec: ModelSpec, n_pages: int, page_size: int, dtype, device):
+        self.page_size = page_size
+        shape = (spec.num_layers, n_pages, page_size, spec.num_kv_heads, spec.head_dim)
+        self.k = torch.zeros(shape, dtype=dtype, device=device)
+        self.v = torch.zeros(shape, dtype=dtype, device=device)
+
+
+class CramEngine:
+    def __init__(self, spec: ModelSpec, weights: Dict[str, torch.Tensor], max_positions: int = 8192):
+        self.spec = spec
+        self.w = weights
+        emb = weights["embed"]
+        self.device, self.dtype = emb.device, emb.dtype
+        if not emb.is_cuda:
+            raise ops.CramError("CramEngine needs CUDA weights: cram_b200 has no CPU fallback")
+        self._rope_len = 0
+        self._ensure_rope(max_positions)
+
+    # ---- construction -------------------------------------------------------------------------------
+    @staticmethod
+    def fuse_state_dict(spec: ModelSpec, sd: Dict[str, torch.Tensor], device, dtype=None) -> Dict[str, torch.Tensor]:
+        """HF Llama/Qwen2 state dict -> fused layout (wqkv, wo, wgu, wdown per layer)."""
+        def g(name):
+            t = sd[name]
+            return t.to(device=device, dtype=dtype or t.dtype)
+        w = {"embed": g("model.embed_tokens.weight"), "norm": g("model.norm.weight")}
+        w["lm_head"] = w["embed"] if spec.tie_embeddings or "lm_head.weight" not in sd else g("lm_head.weight")
+        for l in range(spec.num_layers):
+            p = f"model.layers.{l}."
+            w[f"in_norm.{l}"] = g(p + "input_layernorm.weight")
+            w[f"post_norm.{l}"] = g(p + "post_attention_layernorm.weight")
+            w[f"wqkv.{l}"] = torch.cat([g(p + "self_attn.q_proj.weight"), g(p + "self_attn.k_proj.weight"),
+                                        g(p + "self_attn.v_proj.weight")], 0).contiguous()
+            if spec.qkv_bias and (p + "self_attn.q_proj.bias") in sd:
+                w[f"bqkv.{l}"] = torch.cat([g(p + "self_attn.q_proj.bias"), g(p + "self_attn.k_proj.bias"),
+                                            g(p + "self_attn.v_proj.bias")], 0).contiguous()
+            w[f"wo.{l}"] = g(p + "self_attn.o_proj.weight").contiguous()
+            w[f"wgu.{l}"] = torch.cat([g(p + "mlp.gate_proj.weight"), g(p + "mlp.up_proj.weight")], 0).contiguous()
+            w[f"wdown.{l}"] = g(p + "mlp.down_proj.weight").contiguous()
+        return w
+
+    @classmethod
+    def from_state_dict(cls, spec: ModelSpec, sd, device="cuda", dtype=None, **kw) -> "CramEngine":
+        return cls(spec, cls.fuse_state_dict(spec, sd, device, dtype), **kw)
+
+    @classmethod
+    def from_hf_model(cls, model, device="cuda", **kw) -> "CramEngine":
+        spec = ModelSpec.from_hf(model.config)
+        return cls.from_state_dict(spec, model.state_dict(), device=device, **kw)
+
+    @classmethod
+    def random_init(cls, spec: ModelSpec, seed: int = 0, dtype=torch.bfloat16, device="cuda", std: float = 0.02,
+                    **kw) -> "CramEngine":
+        """Random weights of the given architecture, allocated directly on the device (HF default init N(0, 0.02))."""
+        gen = torch.Generator(device=device)
+        gen.manual_seed(seed)
+
+        def n(*shape):
+            return torch.empty(*shape, dtype=dtype, device=device).normal_(0.0, std, generator=gen)
+
+        H, Hkv, dh, d, f = spec.num_heads, spec.num_kv_heads, spec.head_dim, spec.hidden, spec.intermediate
+        w = {"embed": n(spec.vocab, d), "norm": torch.ones(d, dtype=dtype, device=device)}
+        w["lm_head"] = w["embed"] if spec.tie_embeddings else n(spec.vocab, d)
+        for l in range(spec.num_layers):
+            w[f"in_norm.{l}"] = torch.ones(d, dtype=dtype, device=device)
+            w[f"post_norm.{l}"] = torch.ones(d, dtype=dtype, device=device)
+            w[f"wqkv.{l}"] = n((H + 2 * Hkv) * dh, d)
+            if spec.qkv_bias:
+                w[f"bqkv.{l}"] = n((H + 2 * Hkv) * dh)
+            w[f"wo.{l}"] = n(d, H * dh)
+            w[f"wgu.{l}"] = n(2 * f, d)
+            w[f"wdown.{l}"] = n(d, f)
+        return cls(spec, w, **kw)
+
+    def _ensure_rope(self, n_pos: int) -> None:
+        """cos/sin tables exactly as HF builds them (modeling_llama.py:73-135): fp32 angles, cast to model dtype."""
+        if n_pos <= self._rope_len:
+            return
+        s = self.spec
+        inv_freq = 1.0 / (s.rope_theta ** (torch.arange(0, s.head_dim, 2, dtype=torch.int64).to(torch.float32) / s.head_dim))
+        pos = torch.arange(n_pos, dtype=torch.float32)
+        freqs = pos[:, None] * inv_freq[None, :]
+        emb = torch.cat((freqs, freqs), dim=-1)
+        self.cos = emb.cos().to(self.dtype).to(self.device).contiguous()
+        self.sin = emb.sin().to(self.dtype).to(self.device).contiguous()
+        self._rope_len = n_pos
+
+    # ---- layer pieces -------------------------------------------------------------------------------
+    def _qkv(self, l: int, x: torch.Tensor, pending: Optional[torch.Tensor], positions: torch.Tensor) -> torch.Tensor:
+        s = self.spec
+        h = ops.rmsnorm(x, self.w[f"in_norm.{l}"], s.rms_eps, residual=pending)  # x += pending (in place)
+        qkv = F.linear(h, self.w[f"wqkv.{l}"], self.w.get(f"bqkv.{l}"))
+        ops.rope_(qkv, s.num_heads + s.num_kv_heads, s.head_dim, self.cos, self.sin, positions)
+        return qkv
+
+    def split_qkv(self, qkv: torch.Tensor):
+        s = self.spec
+        a, b = s.num_heads * s.head_dim, (s.num_heads + s.num_kv_heads) * s.head_dim
+        return qkv[:, :a], qkv[:, a:b], qkv[:, b:]
+
+    def layer_post(self, l: int, x: torch.Tensor, attn: torch.Tensor) -> torch.Tensor:
+        """o_proj + residual + MLP of layer l. x is updated in place; returns the pending MLP delta."""
+        s = self.spec
+        o = F.linear(attn, self.w[f"wo.{l}"])
+        h = ops.rmsnorm(x, self.w[f"post_norm.{l}"], s.rms_eps, residual=o)
+        act = ops.silu_mul(F.linear(h, self.w[f"wgu.{l}"]))
+        return F.linear(act, self.w[f"wdown.{l}"])
+
+    # ---- prefill ------------------------------------------------------------------------------------
+    def prefill(self, input_ids: torch.Tensor, cu_seqlens: torch.Tensor, max_seqlen: int,
+                logcred: Optional[torch.Tensor] = None, head_masks: Optional[Sequence[int]] = None,
+                capture: Optional[SweepCapture] = None, kv: Optional[PagedKV] = None,
+                slot_mapping: Optional[torch.Tensor] = None, positions: Optional[torch.Tensor] = None,
+                attn_kernel: int = 0) -> torch.Tensor:
+        """Full forward of packed sequences. Returns the final residual stream [N, hidden] (before the
+        final norm). ``logcred`` is the packed per-key log-credibility [N]; ``head_masks[l]`` the
+        64-bit head bitmask of layer l (0 = untouched layer)."""
+        s = self.spec
+        if positions is None:
+            positions = packed_positions(cu_seqlens, input_ids.numel())
+        self._ensure_rope(max_seqlen)
+        x = F.embedding(input_ids, self.w["embed"])
+        pending = None
+        for l in range(s.num_layers):
+            qkv = self._qkv(l, x, pending, positions)
+            q, k, v = self.split_qkv(qkv)
+            if kv is not None:
+                ops.kv_append(k, v, slot_mapping, kv.k[l], kv.v[l], s.num_kv_heads, s.head_dim)
+            mask = int(head_masks[l]) if (head_masks is not None and logcred is not None) else 0
+            attn = ops.attn_prefill(q, k, v, cu_seqlens, max_seqlen, s.num_heads, s.num_kv_heads, s.head_dim,
+                                    logcred=logcred, head_mask=mask, kernel=attn_kernel)
+            if capture is not None:
+                capture.x_in.append(x.clone())
+                capture.qkv.append(qkv)
+                capture.attn.append(attn)
+            pending = self.layer_post(l, x, attn)
+        x.add_(pending)
+        return x
+
+    def suffix_from_attn(self, l: int, x: torch.Tensor, attn: torch.Tensor, cu_seqlens: torch.Tensor, max_seqlen: int,
+                         positions: torch.Tensor, attn_kernel: int = 0) -> torch.Tensor:
+        """Continue a forward from layer l's attention output (sweep: variants differ from here on).
+        x is the residual stream entering layer l's o_proj add; it is updated in place and returned."""
+        s = self.spec
+        pending = self.layer_post(l, x, attn)
+        for j in range(l + 1, s.num_layers):
+            qkv = self._qkv(j, x, pending, positions)
+            q, k, v = self.split_qkv(qkv)
+            a = ops.attn_prefill(q, k, v, cu_seqlens, max_seqlen, s.num_heads, s.num_kv_heads, s.head_dim,
+                                 kernel=attn_kernel)
+            pending = self.layer_post(j, x, a)
+        x.add_(pending)
+        return x
+
+    def logits(self, x_rows: torch.Tensor) -> torch.Tensor:
+        """Final norm + lm_head on selected rows of the final residual stream."""
+        h = ops.rmsnorm(x_rows.contiguous(), self.w["norm"], self.spec.rms_eps)
+        return F.linear(h, self.w["lm_head"])
+
+    # ---- decode -------------------------------------------------------------------------------------
+    def decode_step(self, tokens: torch.Tensor, positions: torch.Tensor, kv: PagedKV, block_table: torch.Tensor,
+                    seqlens: torch.Tensor, max_seqlen: int, logcred: Optional[torch.Tensor] = None,
+                    bias_len: Optional[torch.Tensor] = None, head_masks: Optional[Sequence[int]] = None,
+                    workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """One token per sequence. positions = index of the new token (int32); seqlens = positions + 1.
+        Returns logits [B, vocab]."""
+        s = self.spec
+        self._ensure_rope(max_seqlen + 1)
+        ps = kv.page_size
+        pos64 = positions.to(torch.int64)
+        slot = block_table.gather(1, (pos64 // ps)[:, None]).squeeze(1).to(torch.int64) * ps + pos64 % ps
+        x = F.embedding(tokens, self.w["embed"])
+        pending = None
+        for l in range(s.num_layers):
+            qkv = self._qkv(l, x, pending, positions)
+            q, k, v = self.split_qkv(qkv)
+            ops.kv_append(k, v, slot, kv.k[l], kv.v[l], s.num_kv_heads, s.head_dim)
+            mask = int(head_masks[l]) if (head_masks is not None and logcred is not None) else 0
+            attn = ops.attn_decode(q, kv.k[l], kv.v[l], block_table, seqlens, max_seqlen, s.num_heads, s.num_kv_heads,
+                                   s.head_dim, logcred=logcred, head_mask=mask, bias_len=bias_len, workspace=workspace)
+            pending = self.layer_post(l, x, attn)
+        x.add_(pending)
+        return self.logits(x)
+
+    @torch.no_grad()
+    def generate(self, prompts: Sequence[torch.Tensor], logcreds: Optional[Sequence[torch.Tensor]] = None,
+                 head_masks: Optional[Sequence[int]] = None, max_new_tokens: int = 100,
+                 eos_token_ids: Sequence[int] = (), bad_token_ids: Sequence[int] = (), page_size: int = 16) -> List[List[int]]:
+        """Greedy generation for a batch of prompts (each a 1-D int64 CUDA tensor) with per-sample
+        credibility. Mirrors model.generate(do_sample=False, max_new_tokens=...) of
+        utils/re_weighting.py:126-132: stop at EOS (the EOS token is kept), single-token bad words are
+        never emitted. Returns the new tokens of every sequence."""
+        s, dev = self.spec, self.device
+        B = len(prompts)
+        lens = [int(p.numel()) for p in prompts]
+        max_total = max(lens) + max_new_tokens
+        pages_per_seq = (max_total + page_size - 1) // page_size
+        kv = PagedKV(s, B * pages_per_seq, page_size, self.dtype, dev)
+        block_table = torch.arange(B * pages_per_seq, dtype=torch.int32, device=dev).view(B, pages_per_seq)
+        cu = torch.zeros(B + 1, dtype=torch.int32)
+        cu[1:] = torch.tensor(lens, dtype=torch.int32).cumsum(0)
+        cu_d = cu.to(dev)
+        ids = torch.cat(list(prompts)).to(dev)
+        positions = packed_positions(cu_d, ids.numel())
+        seq_of_row = torch.repeat_interleave(torch.arange(B, device=dev), torch.tensor(lens, device=dev))
+        pos64 = positions.to(torch.int64)
+        slot = block_table[seq_of_row, pos64 // page_size].to(torch.int64) * page_size + pos64 % page_size
+        lc_packed = torch.cat(list(logcreds)).to(dev) if logcreds is not None else None
+        x = self.prefill(ids, cu_d, max(lens), logcred=lc_packed, head_masks=head_masks, kv=kv, slot_mapping=slot,
+                         positions=positions)
+        last_rows = (cu_d[1:] - 1).to(torch.int64)
+        logits = self.logits(x[last_rows])
+        # decode-time bias: [B, T0max] padded with zeros, keys < bias_len[b] biased
+        lc_dec = bias_len = None
+        if logcreds is not None:
+            lc_dec = torch.zeros(B, max(lens), dtype=lc_packed.dtype, device=dev)
+            for b, lc in enumerate(logcreds):
+                lc_dec[b, :lens[b]] = lc
+            bias_len = torch.tensor(lens, dtype=torch.int32, device=dev)
+        ban = torch.tensor(list(bad_token_ids), dtype=torch.int64, device=dev) if bad_token_ids else None
+        eos = torch.tensor(list(eos_token_ids), dtype=torch.int64, device=dev) if eos_token_ids else None
+        out = [[] for _ in range(B)]
+        alive = [True] * B
+        cur_len = torch.tensor(lens, dtype=torch.int32, device=dev)
+        ws = None
+        for step in range(max_new_tokens):
+            if ban is not None:
+                logits[:, ban] = float("-inf")
+            nxt = logits.argmax(-1)
+            nxt_h = nxt.tolist()
+            for b in range(B):
+                if alive[b]:
+                    out[b].append(nxt_h[b])
+                    if eos is not None and nxt_h[b] in eos_token_ids:
+                        alive[b] = False
+            if not any(alive) or step == max_new_tokens - 1:
+                break
+            positions_d = cur_len.clone()
+            cur_len = cur_len + 1
+            logits = self.decode_step(nxt, positions_d, kv, block_table, cur_len, int(max(lens) + step + 1),
+                                      logcred=lc_dec, bias_len=bias_len, head_masks=head_masks, workspace=ws)
+        return out
+
+
+def packed_positions(cu_seqlens: torch.Tensor, n_rows: int) -> torch.Tensor:
+    """int32 position of every packed row inside its sequence."""
+    dev = cu_seqlens.device
+    lens = (cu_seqlens[1:] - cu_seqlens[:-1]).to(torch.int64)
+    starts = torch.repeat_interleave(cu_seqlens[:-1].to(torch.int64), lens, output_size=n_rows)
+    return (torch.arange(n_rows, device=dev, dtype=torch.int64) - starts).to(torch.int32)

@@ -1,0 +1,133 @@
+"""Head ranking / selection and the IE sweep drivers (reference utils/find_best_heads.py), same
+function names, arguments and JSON formats.
+
+Ranking (:113-150) is host integer/float64 work; it calls the C ABI's cram_rank_heads. Tie rule: the
+reference's np.argsort()[::-1] leaves the order inside groups of exactly equal means to the numpy
+build; here it is defined as value descending, then flat index ascending.
+The drivers (:13-110) keep the heads_scores.json format and the resume-by-length rule.
+"""
+from __future__ import annotations
+
+import json
+import os
+from typing import Dict, List, Sequence, Tuple
+
+import numpy as np
+
+from . import ops
+
+
+def rank_mean_scores(all_scores) -> List[Tuple[float, Tuple[int, int]]]:
+    """[N, L, H] IE samples -> [(mean, (layer, head)), ...] sorted as casual_tracing_combine_all does."""
+    a = np.asarray(all_scores, dtype=np.float64)
+    _, L, H = a.shape
+    order, mean = ops.rank_heads(a)
+    return [(float(mean[i]), (int(order[i]) // H, int(order[i]) % H)) for i in range(order.size)]
+
+
+def select_top_k(ranked: Sequence, topk: int) -> Dict[int, List[int]]:
+    """First k ranked heads -> {layer: [heads...]} in first-seen layer order (:135-146)."""
+    out: Dict[int, List[int]] = {}
+    for _, (l, h) in list(ranked)[:topk]:
+        out.setdefault(l, []).append(h)
+    return out
+
+
+def casual_tracing_combine_all(input_path: str = "datasets/nq/Llama-3"):
+    with open(os.path.join(input_path, "heads_scores.json"), "r", encoding="utf-8") as f:
+        data = json.load(f)
+    ranked = rank_mean_scores(data)
+    with open(os.path.join(input_path, "heads_scores_mean.json"), "w", encoding="utf-8") as f:
+        json.dump(ranked, f, ensure_ascii=False, indent=4)
+    return ranked
+
+
+def find_top_k_heads(input_path: str = "datasets/triviaqa", topk: int = 10):
+    with open(os.path.join(input_path, "heads_scores_mean.json"), "r", encoding="utf-8") as f:
+        data = json.load(f)
+    selected = select_top_k([(v, tuple(i)) for v, i in data], topk)
+    with open(os.path.join(input_path, "selected_heads.json"), "w", encoding="utf-8") as f:
+        json.dump(selected, f, ensure_ascii=False, indent=4)
+    return selected
+
+
+def _model_dir_name(LLM: str) -> str:
+    if "Llama-2-13b" in LLM:
+        return "llama2_13b_chat"
+    if "Llama-3" in LLM:
+        return "llama3"
+    if "Qwen" in LLM:
+        return "qwen"
+    raise UnboundLocalError("cannot access local variable 'model_name'")  # the reference's failure mode
+
+
+def casual_tracing_per_head(filepath: str = "nq_100_bge.json", LLM: str = "Meta-Llama-3-8B-Instruct",
+                            output_dir: str = "datasets/nq", contexts_type: list = ["ori_fake", "reranked_dense"],
+                            topk: int = 4, model=None):
+    """utils/find_best_heads.py:13-58. `model` lets a caller pass a ready Find_Best_Heads (no hub access here)."""
+    with open(filepath, "r", encoding="utf-8") as f:
+        data = json.load(f)
+    model_name = _model_dir_name(LLM)
+    folder = os.path.join(output_dir, model_name)
+    file_path = os.path.join(folder, "heads_scores.json")
+    if os.path.exists(file_path):
+        with open(file_path, "r", encoding="utf8") as file:
+            all_prob_changes = json.load(file)
+    else:
+        all_prob_changes = []
+    if model is None:
+        from .re_weighting import Find_Best_Heads
+        model = Find_Best_Heads(model_name=LLM)
+    for idx, sample in enumerate(data):
+        if idx < len(all_prob_changes):  # resume rule: skip what the file already holds
+            continue
+        contexts, scores = [], []
+        if "ori_fake" in contexts_type:
+            contexts.extend(sample["ori_fake"])
+            scores.extend([0])
+        if "reranked_dense" in contexts_type:
+            contexts.extend(sample["reranked_dense_ctxs"][:topk])
+            scores.extend([1, 1, 1, 1])
+        prob_change = model.cal_logits(question=sample["question"], paras=contexts, scores=scores,
+                                       wrong_answer=sample["wrong answer"])
+        all_prob_changes.append(prob_change)
+        os.makedirs(folder, exist_ok=True)
+        with open(file_path, "w", encoding="utf8") as file:
+            json.dump(all_prob_changes, file, ensure_ascii=False, indent=4)
+    return all_prob_changes
+
+
+def casual_tracing_per_head_with_position(filepath: str = "nq_100_bge.json", LLM: str = "Meta-Llama-3-8B-Instruct",
+                                          output_dir: str = "datasets/nq",
+                                          contexts_type: list = ["ori_fake", "reranked_dense"], topk: int = 4, model=None):
+    """utils/find_best_heads.py:61-110: the fake document moved through the 5 positions."""
+    with open(filepath, "r", encoding="utf-8") as f:
+        data = json.load(f)
+    model_name = _model_dir_name(LLM)
+    if model is None:
+        from .re_weighting import Find_Best_Heads
+        model = Find_Best_Heads(model_name=LLM)
+    all_prob_changes = []
+    folder = os.path.join(output_dir, model_name)
+    for sample in data:
+        per_position = []
+        ori_fake = sample["ori_fake"]
+        ctxs = sample["reranked_dense_ctxs"][:topk]
+        for position in range(5):
+            contexts, scores = [], []
+            if "reranked_dense" in contexts_type:
+                contexts.extend(ctxs[:position])
+                scores.extend([1] * position)
+            if "ori_fake" in contexts_type:
+                contexts.extend(ori_fake)
+                scores.append(0)
+            if "reranked_dense" in contexts_type:
+                contexts.extend(ctxs[position:])
+                scores.extend([1] * (4 - position))
+            per_position.append(model.cal_logits(question=sample["question"], paras=contexts, scores=scores,
+                                                 wrong_answer=sample["wrong answer"]))
+        all_prob_changes.append(per_position)
+        os.makedirs(folder, exist_ok=True)
+        with open(os.path.join(folder, "heads_scores_pos.json"), "w", encoding="utf8") as file:
+            json.dump(all_prob_changes, file, ensure_ascii=False, indent=4)
+    return all_prob_changes

@@ -1,0 +1,124 @@
+"""Kernel (3): batched head-intervention sweep for the indirect effect (IE) of every attention head.
+
+The reference (Find_Best_Heads.cal_logits, utils/re_weighting.py:152-175) runs 1 + L*H full forwards
+per prompt. Here one clean forward is cached per prompt (SweepCapture); for layer l the H single-head
+variants share that layer's input, so ONE all-heads-biased attention launch + a head-splice kernel
+builds them and the suffix layers l+1..L-1 run once over the batch of variants; the answer-token
+logits come from a fused epilogue (final norm + the answer rows of lm_head + sum + IE) and a single
+device->host copy per prompt replaces L*H ``.item()`` syncs.
+
+Multi-GPU: every rank holds a model replica and the clean forward; for EVERY
+layer rank r takes heads {h : h mod N == r} (cost is proportional to L - l, so splitting inside each
+layer balances exactly); one all_gather of f32[L*H/N] per prompt assembles the matrix. The reduction
+order does not depend on N, so sharded == unsharded bit for bit.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import ops
+from .engine import CramEngine, SweepCapture
+
+
+def heads_of_rank(n_heads: int, rank: int, world_size: int) -> List[int]:
+    """Heads rank `rank` sweeps in every layer: h mod world_size == rank."""
+    return [h for h in range(n_heads) if h % world_size == rank]
+
+
+def assemble_gathered(gathered: Sequence[torch.Tensor], n_layers: int, n_heads: int, world_size: int) -> torch.Tensor:
+    """Inverse of the head partition: gathered[r] is rank r's [L, len(heads_of_rank(r))] slice (padded to the
+    widest rank with NaN when H % N != 0)."""
+    out = torch.full((n_layers, n_heads), float("nan"), dtype=gathered[0].dtype, device=gathered[0].device)
+    for r in range(world_size):
+        hs = heads_of_rank(n_heads, r, world_size)
+        if hs:
+            out[:, hs] = gathered[r][:, :len(hs)]
+    return out
+
+
+class IESweep:
+    def __init__(self, engine: CramEngine, rank: int = 0, world_size: int = 1, group=None,
+                 max_rows: int = 1 << 17, attn_kernel: int = 0):
+        self.engine = engine
+        self.rank, self.world_size, self.group = rank, world_size, group
+        self.max_rows = max_rows
+        self.attn_kernel = attn_kernel
+
+    @torch.no_grad()
+    def clean_pass(self, input_ids: torch.Tensor, answer_ids: torch.Tensor):
+        """One clean forward; returns (capture, ori) with ori the device scalar of re_weighting.py:160."""
+        eng = self.engine
+        T = input_ids.numel()
+        cu = torch.tensor([0, T], dtype=torch.int32, device=input_ids.device)
+        cap = SweepCapture()
+        x = eng.prefill(input_ids, cu, T, capture=cap, attn_kernel=self.attn_kernel)
+        n = answer_ids.numel()
+        ori, _ = ops.sweep_answer_ie(x[T - n:].contiguous()[None], eng.w["norm"], eng.spec.rms_eps, eng.w["lm_head"],
+                                     answer_ids, None)
+        return cap, ori
+
+    @torch.no_grad()
+    def sweep_layer(self, cap: SweepCapture, l: int, heads: Sequence[int], logcred: torch.Tensor,
+                    answer_ids: torch.Tensor, ori: torch.Tensor) -> torch.Tensor:
+        """IE of `heads` of layer l -> f32 [len(heads)] on the device."""
+        eng, s = self.engine, self.engine.spec
+        dev = logcred.device
+        T = cap.x_in[l].shape[0]
+        n = answer_ids.numel()
+        cu1 = torch.tensor([0, T], dtype=torch.int32, device=dev)
+        q, k, v = eng.split_qkv(cap.qkv[l])
+        biased = ops.attn_prefill(q, k, v, cu1, T, s.num_heads, s.num_kv_heads, s.head_dim, logcred=logcred,
+                                  head_mask=ops.heads_to_mask(heads), kernel=self.attn_kernel)
+        out = torch.empty(len(heads), dtype=torch.float32, device=dev)
+        per_chunk = max(1, self.max_rows // T)
+        for c0 in range(0, len(heads), per_chunk):
+            hs = list(heads[c0:c0 + per_chunk])
+            nv = len(hs)
+            hs_t = torch.tensor(hs, dtype=torch.int32, device=dev)
+            variants = ops.sweep_splice_heads(cap.attn[l], biased, hs_t, s.num_heads, s.head_dim)
+            x = cap.x_in[l].repeat(nv, 1)
+            cu = torch.arange(nv + 1, dtype=torch.int32, device=dev) * T
+            pos = torch.arange(T, dtype=torch.int32, device=dev).repeat(nv)
+            x = eng.suffix_from_attn(l, x, variants.view(nv * T, -1), cu, T, pos, attn_kernel=self.attn_kernel)
+            tail = x.view(nv, T, s.hidden)[:, T - n:].contiguous()
+            _, ie = ops.sweep_answer_ie(tail, eng.w["norm"], s.rms_eps, eng.w["lm_head"], answer_ids, ori)
+            out[c0:c0 + nv] = ie
+        return out
+
+    @torch.no_grad()
+    def local_ie(self, input_ids: torch.Tensor, logcred: torch.Tensor, answer_ids: torch.Tensor,
+                 layers: Optional[Sequence[int]] = None) -> torch.Tensor:
+        """This rank's slice [L, ceil(H/N)] (f32, device): column i is head rank + N*i; NaN where not swept."""
+        s = self.engine.spec
+        layers = list(range(s.num_layers)) if layers is None else list(layers)
+        cap, ori = self.clean_pass(input_ids, answer_ids)
+        self.last_ori = ori
+        mine = heads_of_rank(s.num_heads, self.rank, self.world_size)
+        width = (s.num_heads + self.world_size - 1) // self.world_size
+        local = torch.full((s.num_layers, width), float("nan"), dtype=torch.float32, device=input_ids.device)
+        if mine:
+            for l in layers:
+                local[l, :len(mine)] = self.sweep_layer(cap, l, mine, logcred, answer_ids, ori)
+        return local
+
+    def gather(self, local: torch.Tensor) -> torch.Tensor:
+        """The path's only collective: one all_gather of the per-rank IE slices -> [L, H] on every rank."""
+        s = self.engine.spec
+        return gather_ie(local, s.num_layers, s.num_heads, self.world_size, self.group)
+
+    @torch.no_grad()
+    def cal_ie(self, input_ids: torch.Tensor, logcred: torch.Tensor, answer_ids: torch.Tensor,
+               layers: Optional[Sequence[int]] = None) -> torch.Tensor:
+        """IE matrix [L, H] (f32, device) for one prompt; rows of layers not in `layers` are NaN."""
+        return self.gather(self.local_ie(input_ids, logcred, answer_ids, layers))
+
+
+def gather_ie(local: torch.Tensor, n_layers: int, n_heads: int, world_size: int, group=None) -> torch.Tensor:
+    if world_size == 1:
+        return assemble_gathered([local], n_layers, n_heads, 1)
+    import torch.distributed as dist
+    gathered = [torch.empty_like(local) for _ in range(world_size)]
+    dist.all_gather(gathered, local.contiguous(), group=group)
+    return assemble_gathered(gathered, n_layers, n_heads, world_size)
