@@ -103,8 +103,11 @@ __global__ void rope_kernel(T* __restrict__ qk, int64_t row_stride, int64_t n_ro
 #pragma unroll
     for (int e = 0; e < N; ++e) {
       const float a = DType<T>::to_f(x1.v[e]), b = DType<T>::to_f(x2.v[e]);
-      o1.v[e] = DType<T>::from_f(round_to<T>(a * DType<T>::to_f(c1.v[e])) + round_to<T>(-b * DType<T>::to_f(s1.v[e])));
-      o2.v[e] = DType<T>::from_f(round_to<T>(b * DType<T>::to_f(c2.v[e])) + round_to<T>(a * DType<T>::to_f(s2.v[e])));
+      // explicit _rn intrinsics: no FMA contraction, so fp32 also matches torch's mul, mul, add
+      o1.v[e] = DType<T>::from_f(__fadd_rn(round_to<T>(__fmul_rn(a, DType<T>::to_f(c1.v[e]))),
+                                           round_to<T>(__fmul_rn(-b, DType<T>::to_f(s1.v[e])))));
+      o2.v[e] = DType<T>::from_f(__fadd_rn(round_to<T>(__fmul_rn(b, DType<T>::to_f(c2.v[e]))),
+                                           round_to<T>(__fmul_rn(a, DType<T>::to_f(s2.v[e])))));
     }
     stvec(base + j, o1);
     stvec(base + j + half, o2);

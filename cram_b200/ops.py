@@ -18,6 +18,8 @@ _DT = {torch.float32: CRAM_F32, torch.float16: CRAM_F16, torch.bfloat16: CRAM_BF
 
 # counts launches of OUR kernels (bench.py reports it as gpu_launches)
 launch_count = 0
+# when a list, attn_prefill appends a (start, end) CUDA-event pair per launch, recorded on the launching stream
+attn_events = None
 
 
 def dtype_code(dt: torch.dtype) -> int:
@@ -126,7 +128,13 @@ def attn_prefill(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens_q
     p.bias_len = _ptr(bias_len)
     p.causal = 1 if causal else 0
     p.kernel = kernel
+    if attn_events is not None:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
     check(lib.cram_attn_prefill(C.byref(p), _stream()), "cram_attn_prefill")
+    if attn_events is not None:
+        ev1.record()
+        attn_events.append((ev0, ev1))
     launch_count += 1
     return (out, lse) if return_lse else out
 

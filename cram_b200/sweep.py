@@ -40,9 +40,13 @@ def assemble_gathered(gathered: Sequence[torch.Tensor], n_layers: int, n_heads: 
 
 class IESweep:
     def __init__(self, engine: CramEngine, rank: int = 0, world_size: int = 1, group=None,
-                 max_rows: int = 1 << 17, attn_kernel: int = 0):
+                 variant_chunk: int = 4, max_rows: int = 1 << 17, attn_kernel: int = 0):
+        """variant_chunk: how many single-head variants go through the suffix layers per batch. It is
+        FIXED (not "all of this rank's heads") so every GEMM sees the same M whatever the rank count;
+        that is what makes the sharded sweep bit-identical to the unsharded one."""
         self.engine = engine
         self.rank, self.world_size, self.group = rank, world_size, group
+        self.variant_chunk = variant_chunk
         self.max_rows = max_rows
         self.attn_kernel = attn_kernel
 
@@ -72,7 +76,7 @@ class IESweep:
         biased = ops.attn_prefill(q, k, v, cu1, T, s.num_heads, s.num_kv_heads, s.head_dim, logcred=logcred,
                                   head_mask=ops.heads_to_mask(heads), kernel=self.attn_kernel)
         out = torch.empty(len(heads), dtype=torch.float32, device=dev)
-        per_chunk = max(1, self.max_rows // T)
+        per_chunk = max(1, min(self.variant_chunk, self.max_rows // T))
         for c0 in range(0, len(heads), per_chunk):
             hs = list(heads[c0:c0 + per_chunk])
             nv = len(hs)

@@ -1,0 +1,144 @@
+"""GPU: kernel (1) prefill through the C ABI -- generic and tcgen05 kernels vs the oracle and vs each other."""
+import numpy as np
+import pytest
+import torch
+
+from cram_b200 import ops
+from oracle import cram_oracle as orc
+from tests.helpers import cu_of, make_logcred, make_qkv, ref_attention, report
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+GENERIC, SM100 = 1, 2
+
+
+def _oracle_hooked_eager(q, k, v, T, H, Hkv, dh, logcred, heads):
+    """The reference arithmetic itself: edit_attention_mask + HF eager attention (oracle, CPU)."""
+    dt = q.dtype
+    qc = q.cpu().view(1, T, H, dh).transpose(1, 2)
+    kc = k.cpu().view(1, T, Hkv, dh).transpose(1, 2)
+    vc = v.cpu().view(1, T, Hkv, dh).transpose(1, 2)
+    base = torch.triu(torch.full((T, T), torch.finfo(dt).min, dtype=dt), diagonal=1)[None, None]
+    mask = orc.edit_attention_mask(base, logcred.cpu().view(1, T), heads, H, T, T, dt)
+    return orc.eager_attention(qc, kc, vc, mask, dh ** -0.5).reshape(T, H * dh)
+
+
+@pytest.mark.parametrize("dtype,dh,tol", [(torch.float32, 64, 2e-5), (torch.float32, 40, 2e-5), (torch.bfloat16, 128, 2e-2)])
+def test_generic_vs_oracle_hooked_eager(dtype, dh, tol):
+    T, H, Hkv = 333, 4, 2
+    q, k, v, _ = make_qkv(T, H, Hkv, dh, dtype, DEV, seed=1)
+    lc = make_logcred([T], DEV, dtype, seed=2)
+    for heads in ([], [1], [0, 3], [0, 1, 2, 3]):
+        got = ops.attn_prefill(q, k, v, cu_of([T], DEV), T, H, Hkv, dh, logcred=lc, head_mask=ops.heads_to_mask(heads),
+                               kernel=GENERIC)
+        want = _oracle_hooked_eager(q, k, v, T, H, Hkv, dh, lc, heads)
+        err = report(f"generic {dtype} dh={dh} heads={heads}", got.cpu().float(), want.float())
+        assert err <= tol
+        assert not torch.isnan(got).any()
+
+
+SM100_CASES = [
+    # lens, H, Hkv, dh
+    ([128], 4, 2, 128),
+    ([256], 4, 4, 64),
+    ([333], 4, 2, 128),
+    ([1, 127, 129, 500, 64], 8, 2, 128),
+    ([1000, 77], 4, 1, 64),
+    ([2048], 8, 2, 128),
+]
+
+
+@pytest.mark.parametrize("lens,H,Hkv,dh", SM100_CASES)
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_sm100_vs_reference(lens, H, Hkv, dh, dtype):
+    total = sum(lens)
+    q, k, v, _ = make_qkv(total, H, Hkv, dh, dtype, DEV, seed=5)
+    cu = cu_of(lens, DEV)
+    lc = make_logcred(lens, DEV, dtype, seed=6)
+    for mask in (0, 0b10, (1 << H) - 1):
+        got, lse = ops.attn_prefill(q, k, v, cu, max(lens), H, Hkv, dh, logcred=lc, head_mask=mask, kernel=SM100,
+                                    return_lse=True)
+        want = ref_attention(q, k, v, cu, None, H, Hkv, dh, logcred=lc, head_mask=mask)
+        err = report(f"sm100 {dtype} lens={lens} H={H}/{Hkv} dh={dh} mask={mask:b}", got, want)
+        assert not torch.isnan(got).any()
+        assert err <= 2e-2
+        gen, lse_g = ops.attn_prefill(q, k, v, cu, max(lens), H, Hkv, dh, logcred=lc, head_mask=mask, kernel=GENERIC,
+                                      return_lse=True)
+        assert report("  vs generic", got, gen) <= 2e-2
+        fin = torch.isfinite(lse_g)
+        assert torch.equal(fin, torch.isfinite(lse))
+        assert (lse[fin] - lse_g[fin]).abs().max().item() <= 2e-2
+
+
+def test_sm100_small_vs_oracle_hooked_eager():
+    """Same inputs through the reference's own arithmetic (bf16 eager + dense hooked mask)."""
+    T, H, Hkv, dh = 384, 4, 2, 128
+    q, k, v, _ = make_qkv(T, H, Hkv, dh, torch.bfloat16, DEV, seed=9)
+    lc = make_logcred([T], DEV, torch.bfloat16, seed=10)
+    for heads in ([], [2], [0, 1, 2, 3]):
+        got = ops.attn_prefill(q, k, v, cu_of([T], DEV), T, H, Hkv, dh, logcred=lc, head_mask=ops.heads_to_mask(heads),
+                               kernel=SM100)
+        want = _oracle_hooked_eager(q, k, v, T, H, Hkv, dh, lc, heads)
+        assert report(f"sm100 vs oracle eager heads={heads}", got.cpu().float(), want.float()) <= 2e-2
+
+
+def test_sm100_properties_full_size():
+    """Llama-3-8B layer shape, T = 2048 x 4 sequences: properties that need no oracle."""
+    H, Hkv, dh = 32, 8, 128
+    lens = [2048, 2011, 1987, 2048]
+    total = sum(lens)
+    q, k, v, _ = make_qkv(total, H, Hkv, dh, torch.bfloat16, DEV, seed=11)
+    cu = cu_of(lens, DEV)
+    lc = make_logcred(lens, DEV, torch.bfloat16, seed=12)
+    mask = 0x0F0F00FF
+    clean = ops.attn_prefill(q, k, v, cu, 2048, H, Hkv, dh, kernel=SM100)
+    biased = ops.attn_prefill(q, k, v, cu, 2048, H, Hkv, dh, logcred=lc, head_mask=mask, kernel=SM100)
+    cv, bv = clean.view(total, H, dh), biased.view(total, H, dh)
+    for h in range(H):
+        if not (mask >> h) & 1:
+            assert torch.equal(cv[:, h], bv[:, h]), h  # untouched heads are bit-identical
+    assert not torch.equal(cv[:, 0], bv[:, 0])
+    # zero log-credibility == clean
+    zero = ops.attn_prefill(q, k, v, cu, 2048, H, Hkv, dh, logcred=torch.zeros_like(lc), head_mask=mask, kernel=SM100)
+    assert torch.equal(zero, clean)
+    # V = 1 -> every output is exactly the probability mass = 1
+    ones = torch.ones_like(v)
+    o = ops.attn_prefill(q, k, ones, cu, 2048, H, Hkv, dh, logcred=lc, head_mask=mask, kernel=SM100)
+    assert (o.float() - 1).abs().max().item() <= 8e-3
+    # run-to-run determinism
+    again = ops.attn_prefill(q, k, v, cu, 2048, H, Hkv, dh, logcred=lc, head_mask=mask, kernel=SM100)
+    assert torch.equal(again, biased)
+    # spot check against fp64 on two sequences' worth of heads
+    want = ref_attention(q, k, v, cu, None, H, Hkv, dh, logcred=lc, head_mask=mask)
+    assert report("sm100 8B-shape", biased, want) <= 2e-2
+
+
+def test_chunked_prefill_and_bias_len():
+    """len_q < len_k (queries are the tail of the keys) and a bias that covers only the prompt part."""
+    H, Hkv, dh = 4, 2, 128
+    lens_k, lens_q = [300, 513], [44, 129]
+    q, _, _, _ = make_qkv(sum(lens_q), H, Hkv, dh, torch.bfloat16, DEV, seed=21)
+    _, k, v, _ = make_qkv(sum(lens_k), H, Hkv, dh, torch.bfloat16, DEV, seed=22)
+    lc = make_logcred(lens_k, DEV, torch.bfloat16, seed=23)
+    bl = torch.tensor([250, 400], dtype=torch.int32, device=DEV)
+    cuq, cuk = cu_of(lens_q, DEV), cu_of(lens_k, DEV)
+    want = ref_attention(q, k, v, cuq, cuk, H, Hkv, dh, logcred=lc, head_mask=0b0110, bias_len=bl.tolist())
+    for kern in (GENERIC, SM100):
+        got = ops.attn_prefill(q, k, v, cuq, max(lens_q), H, Hkv, dh, logcred=lc, head_mask=0b0110, cu_seqlens_k=cuk,
+                               max_seqlen_k=max(lens_k), bias_len=bl, kernel=kern)
+        assert report(f"chunked kernel={kern}", got, want) <= 2e-2
+
+
+def test_all_keys_zero_credibility_row_is_defined():
+    """A row whose every visible key has credibility 0 (log = -inf): output defined as 0, never NaN."""
+    T, H, Hkv, dh = 130, 2, 1, 64
+    q, k, v, _ = make_qkv(T, H, Hkv, dh, torch.bfloat16, DEV, seed=31)
+    lc = torch.full((T,), float("-inf"), dtype=torch.bfloat16, device=DEV)
+    lc[100:] = 0
+    for kern in (GENERIC, SM100):
+        got = ops.attn_prefill(q, k, v, cu_of([T], DEV), T, H, Hkv, dh, logcred=lc, head_mask=0b01, kernel=kern)
+        g = got.view(T, H, dh)
+        assert not torch.isnan(got).any()
+        assert (g[:100, 0] == 0).all() and (g[100:, 0] != 0).any()
+        want = ref_attention(q, k, v, cu_of([T], DEV), None, H, Hkv, dh, logcred=lc, head_mask=0b01)
+        assert report(f"zero-cred kernel={kern}", got, want) <= 2e-2

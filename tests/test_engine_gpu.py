@@ -1,0 +1,127 @@
+"""GPU: the whole path on the tiny model of BASELINE configs[0] vs the golden vectors the UNMODIFIED
+reference produced (tests/golden/tiny_model.npz) and vs the oracle in bf16."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from cram_b200 import ops, synth
+from cram_b200.engine import CramEngine, ModelSpec
+from cram_b200.re_weighting import Find_Best_Heads, Re_Weighting_Strategy
+from oracle import cram_oracle as orc
+from oracle.tiny_model import TINY_SPEC, tiny_state_dict
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+HEAD_SETS = {"none": None, "l0h1": {0: [1]}, "l1h03": {1: [0, 3]}, "all": {0: [0, 1, 2, 3], 1: [0, 1, 2, 3]},
+             "strkeys": {"1": [2], "0": [0]}}
+
+
+def _spec():
+    t = TINY_SPEC
+    return ModelSpec(t.num_layers, t.num_heads, t.num_kv_heads, t.head_dim, t.hidden, t.intermediate, t.vocab, t.rms_eps,
+                     t.rope_theta)
+
+
+@pytest.fixture(scope="module")
+def gold(golden_dir):
+    g = np.load(os.path.join(golden_dir, "tiny_model.npz"))
+    meta = json.load(open(os.path.join(golden_dir, "tiny_model_meta.json")))
+    return g, meta
+
+
+@pytest.fixture(scope="module")
+def engine32():
+    return CramEngine.from_state_dict(_spec(), tiny_state_dict(torch.float32), device=DEV)
+
+
+def _masks(hs, L=2):
+    m = [0] * L
+    for l, heads in (hs or {}).items():
+        m[int(l)] |= ops.heads_to_mask(heads)
+    return m
+
+
+def test_fp32_logits_match_reference_golden(gold, engine32):
+    g, meta = gold
+    ids = torch.from_numpy(g["input_ids"]).to(DEV)
+    T = ids.numel()
+    cu = torch.tensor([0, T], dtype=torch.int32, device=DEV)
+    cred = torch.from_numpy(g["cred_bits"].view(np.float16).copy()).to(DEV)
+    logcred = ops.log_cred(cred, torch.float32)
+    rows = torch.from_numpy(g["logit_rows"]).to(DEV)
+    for name, hs in HEAD_SETS.items():
+        x = engine32.prefill(ids, cu, T, logcred=logcred, head_masks=_masks(hs))
+        lg = engine32.logits(x[rows]).cpu().numpy()
+        err = np.abs(lg - g[f"logits_{name}"]).max()
+        print(f"[tiny fp32 logits {name}] max_abs={err:.3e} (|logit| max {np.abs(lg).max():.2f})")
+        assert err <= 5e-4, name
+    # the hook must actually move the logits (guards against a silently ignored bias)
+    assert np.abs(g["logits_all"] - g["logits_none"]).max() > 1e-2
+
+
+def test_drop_in_api_span_generate_and_ie(gold, engine32):
+    g, meta = gold
+    tok = synth.load_tokenizer()
+    for name, hs in HEAD_SETS.items():
+        rw = Re_Weighting_Strategy("tiny-llama", layers_to_be_modified=dict(hs) if hs else dict(), tokenizer=tok,
+                                   engine=engine32)
+        if name == "none":
+            rw.layers_to_be_modified = {}
+        inputs, w = rw.decode_with_special_attention(question=meta["question"], paras=meta["paras"], scores=meta["scores"])
+        assert np.array_equal(inputs["input_ids"][0].cpu().numpy(), g["input_ids"])
+        assert w.dtype == torch.float16 and tuple(w.shape) == (1, len(g["input_ids"]))
+        assert np.array_equal(w[0].cpu().view(torch.int16).numpy().view(np.uint16), g["cred_bits"])  # bit-exact
+        prompt, out = rw.run_RAG_with_attention_weighting(question=meta["question"], paras=meta["paras"],
+                                                          scores=meta["scores"])
+        assert out == str(g[f"gen_text_{name}"]), (name, out, str(g[f"gen_text_{name}"]))
+        # greedy tokens (first 8) against the reference's own generate
+        masks = _masks(rw.layers_to_be_modified)
+        new = engine32.generate([inputs["input_ids"][0]], [ops.log_cred(w[0], torch.float32)], masks, max_new_tokens=8,
+                                eos_token_ids=[tok.eos_token_id])[0]
+        assert new == g[f"greedy_{name}"].tolist()[:len(new)], name
+    # a passage that is not in the prompt verbatim fails like the reference (TypeError at re_weighting.py:111)
+    rw = Re_Weighting_Strategy("tiny-llama", tokenizer=tok, engine=engine32)
+    with pytest.raises(TypeError):
+        rw.decode_with_special_attention(question="q?", paras=["abc\ndef"], scores=[0.5])
+
+    fb = Find_Best_Heads("tiny-llama", tokenizer=tok, engine=engine32)
+    ie = np.array(fb.cal_logits(question=meta["question"], paras=meta["paras"], scores=meta["sweep_scores"],
+                                wrong_answer=meta["wrong"]))
+    print("[tiny fp32 IE]\n", ie, "\n", g["ie_ref"])
+    assert ie.shape == g["ie_ref"].shape
+    assert np.abs(ie - g["ie_ref"]).max() <= 1e-3
+    assert abs(float(fb.ori_prob_sum) - float(g["ie_ori_logit_sum"])) <= 1e-3
+    # ranking of the heads by IE is the reference's
+    assert np.argsort(-ie.flatten(), kind="stable").tolist() == np.argsort(-g["ie_ref"].flatten(), kind="stable").tolist()
+
+
+def test_bf16_tracks_oracle_bf16_within_bf16_noise(gold):
+    """bf16 engine vs the oracle's bf16 hooked-eager forward: our error against the fp32 truth must be
+    no worse than the reference arithmetic's own bf16 error (x2 margin)."""
+    g, meta = gold
+    ids_np = g["input_ids"][:320]
+    sd16 = tiny_state_dict(torch.bfloat16)
+    eng = CramEngine.from_state_dict(_spec(), sd16, device=DEV)
+    ids = torch.from_numpy(ids_np).to(DEV)
+    T = ids.numel()
+    cu = torch.tensor([0, T], dtype=torch.int32, device=DEV)
+    cred16 = torch.from_numpy(g["cred_bits"].view(np.float16)[:320].copy())
+    lc_bf = orc.log_chain(cred16.numpy(), torch.bfloat16)
+    hooks = {0: (lc_bf[None], [1, 2]), 1: (lc_bf[None], [0, 3])}
+    with torch.no_grad():
+        want16 = orc.llama_forward(sd16, TINY_SPEC, torch.from_numpy(ids_np)[None], hooks)[0].float()
+        sd32 = {k: v.float() for k, v in sd16.items()}
+        truth = orc.llama_forward(sd32, TINY_SPEC, torch.from_numpy(ids_np)[None],
+                                  {l: (lc.float(), h) for l, (lc, h) in hooks.items()})[0]
+    for kern in (1, 2):
+        x = eng.prefill(ids, cu, T, logcred=lc_bf.to(DEV), head_masks=[0b0110, 0b1001], attn_kernel=kern)
+        got = eng.logits(x).float().cpu()
+        e_ours, e_ref = (got - truth).abs().max().item(), (want16 - truth).abs().max().item()
+        d = (got - want16).abs().max().item()
+        print(f"[tiny bf16 kernel={kern}] ours-vs-fp32 {e_ours:.3e}  oracle-bf16-vs-fp32 {e_ref:.3e}  ours-vs-oracle-bf16 {d:.3e}")
+        assert e_ours <= 2 * e_ref + 1e-2
+        agree = (got.argmax(-1) == want16.argmax(-1)).float().mean().item()
+        assert agree >= 0.97

@@ -1,0 +1,89 @@
+"""GPU: the HBM-bound glue kernels vs the HF eager formulas evaluated by torch on the same device."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from cram_b200 import ops
+from oracle import cram_oracle as orc
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+def test_rmsnorm_and_residual(dtype):
+    torch.manual_seed(0)
+    x = torch.randn(37, 4096, device=DEV).to(dtype)
+    r = torch.randn(37, 4096, device=DEV).to(dtype)
+    w = (1 + 0.1 * torch.randn(4096, device=DEV)).to(dtype)
+    want = orc.rmsnorm(x, w, 1e-5)
+    got = ops.rmsnorm(x.clone(), w, 1e-5)
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    assert (got.float() - want.float()).abs().max().item() <= tol
+    if dtype != torch.float32:  # identical up to the rounding of one rsqrt ulp: the bulk must be bit-equal
+        assert (got == want).float().mean().item() > 0.98
+    x2 = x.clone()
+    got2 = ops.rmsnorm(x2, w, 1e-5, residual=r)
+    assert torch.equal(x2, x + r)  # the fused residual add is the exact model-dtype add
+    assert (got2.float() - orc.rmsnorm(x + r, w, 1e-5).float()).abs().max().item() <= tol * 2
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_rope_matches_hf(dtype):
+    torch.manual_seed(1)
+    H, Hkv, dh, N = 8, 2, 128, 300
+    spec = orc.ModelSpec(1, H, Hkv, dh, 64, 64, 10, rope_theta=500000.0)
+    qkv = torch.randn(N, (H + 2 * Hkv) * dh, device=DEV).to(dtype)
+    pos = torch.randint(0, 4000, (N,), device=DEV, dtype=torch.int32)
+    cos_t, sin_t = orc.rope_cos_sin(spec, torch.arange(4096)[None], dtype)
+    cos_t, sin_t = cos_t[0].to(DEV).contiguous(), sin_t[0].to(DEV).contiguous()
+    want = qkv.clone()
+    for name, h0, n in (("q", 0, H), ("k", H, Hkv)):
+        t = qkv[:, h0 * dh:(h0 + n) * dh].view(N, n, dh)
+        c, s = cos_t[pos.long()][:, None], sin_t[pos.long()][:, None]
+        want[:, h0 * dh:(h0 + n) * dh] = (t * c + orc.rotate_half(t) * s).reshape(N, n * dh)
+    got = qkv.clone()
+    ops.rope_(got, H + Hkv, dh, cos_t, sin_t, pos)
+    assert torch.equal(got[:, (H + Hkv) * dh:], qkv[:, (H + Hkv) * dh:])  # V untouched
+    assert torch.equal(got, want)  # same three roundings as HF -> bit-exact
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_silu_mul(dtype):
+    torch.manual_seed(2)
+    gu = (torch.randn(65, 2 * 1024, device=DEV) * 3).to(dtype)
+    want = F.silu(gu[:, :1024]) * gu[:, 1024:]
+    got = ops.silu_mul(gu)
+    if dtype == torch.float32:
+        assert (got - want).abs().max().item() <= 1e-5
+    else:
+        assert (got == want).float().mean().item() > 0.995
+        assert (got.float() - want.float()).abs().max().item() <= 0.07
+
+
+def test_splice_and_answer_ie():
+    torch.manual_seed(3)
+    T, H, dh, hidden, V, n = 50, 4, 64, 256, 1000, 3
+    clean = torch.randn(T, H * dh, device=DEV).bfloat16()
+    biased = torch.randn(T, H * dh, device=DEV).bfloat16()
+    heads = torch.tensor([2, 0, 3], dtype=torch.int32, device=DEV)
+    out = ops.sweep_splice_heads(clean, biased, heads, H, dh)
+    for i, h in enumerate(heads.tolist()):
+        want = clean.clone()
+        want[:, h * dh:(h + 1) * dh] = biased[:, h * dh:(h + 1) * dh]
+        assert torch.equal(out[i], want)
+    for dtype in (torch.float32, torch.bfloat16):
+        x = torch.randn(3, T, hidden, device=DEV).to(dtype)
+        nw = (1 + 0.1 * torch.randn(hidden, device=DEV)).to(dtype)
+        lm = (torch.randn(V, hidden, device=DEV) * 0.06).to(dtype)
+        ans = torch.tensor([5, 999, 17], dtype=torch.int64, device=DEV)
+        tail = x[:, T - n:].contiguous()
+        cur0, _ = ops.sweep_answer_ie(tail[:1], nw, 1e-5, lm, ans, None)
+        cur, ie = ops.sweep_answer_ie(tail, nw, 1e-5, lm, ans, cur0)
+        logits = F.linear(orc.rmsnorm(x, nw, 1e-5), lm)  # [3, T, V]
+        for v in range(3):
+            want = orc.answer_logit_sum(logits[v:v + 1].cpu(), ans.cpu())
+            tol = 1e-4 if dtype == torch.float32 else 0.05
+            assert abs(cur[v].item() - float(want)) <= tol, (dtype, v, cur[v].item(), float(want))
+        assert ie[0].item() == 0.0
+        assert torch.allclose(ie, (cur0 - cur).to(dtype).float(), atol=1e-6)
