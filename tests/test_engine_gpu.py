@@ -82,10 +82,12 @@ def test_drop_in_api_span_generate_and_ie(gold, engine32):
         new = engine32.generate([inputs["input_ids"][0]], [ops.log_cred(w[0], torch.float32)], masks, max_new_tokens=8,
                                 eos_token_ids=[tok.eos_token_id])[0]
         assert new == g[f"greedy_{name}"].tolist()[:len(new)], name
-    # a passage that is not in the prompt verbatim fails like the reference (TypeError at re_weighting.py:111)
+    # a passage that is not in the prompt verbatim (e.g. a chat template that rewrites whitespace) makes the
+    # reference fail with TypeError at re_weighting.py:111; the kernel reports it and the class raises the same
     rw = Re_Weighting_Strategy("tiny-llama", tokenizer=tok, engine=engine32)
+    rw._build_prompt = lambda q_, p_, a_: ("Given the following information: \nPassage-0: something else\nAnswer: ", True)
     with pytest.raises(TypeError):
-        rw.decode_with_special_attention(question="q?", paras=["abc\ndef"], scores=[0.5])
+        rw.decode_with_special_attention(question="q?", paras=["abc def"], scores=[0.5])
 
     fb = Find_Best_Heads("tiny-llama", tokenizer=tok, engine=engine32)
     ie = np.array(fb.cal_logits(question=meta["question"], paras=meta["paras"], scores=meta["sweep_scores"],
