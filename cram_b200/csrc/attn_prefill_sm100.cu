@@ -1,10 +1,11 @@
-// Kernel (1): fused credibility-biased FlashAttention-style prefill for sm_100a.
+// Kernel (1): fused credibility-biased FlashAttention-style prefill for sm_100a (v2: two query tiles
+// per CTA, ping-pong softmax warpgroups).
 //
 //   S = Q K^T      tcgen05.mma (SS), 128x128 fp32 accumulator in TMEM, operands TMA-staged in
 //                  128B-swizzled shared memory
 //   online softmax one thread per query row straight out of TMEM (tcgen05.ld 32x32b); the per-key
 //                  log-credibility bias (already x log2e, with the key-length mask folded in as
-//                  -inf) is one FFMA: t = S*scale*log2e + bias[k]
+//                  -inf) is one packed FFMA2: t = S*scale*log2e + bias[k]
 //   O += P V       tcgen05.mma (TS): P is written back to TMEM as bf16/fp16 over the S columns and
 //                  consumed as the A operand; V is the MN-major B operand from shared memory
 //
@@ -13,13 +14,16 @@
 // touch HBM. Biasing head h by logcred[k] before the softmax equals multiplying its probabilities
 // by cred[k] and renormalising (README.md:21).
 //
-// CTA = 128 query rows of one (sequence, head); 6 warps:
-//   warps 0-3  softmax + correction + epilogue (TMEM lanes 32w..32w+31)
-//   warp  4    producer: TMA loads of Q, K[j], V[j]; builds the per-tile bias vector
-//   warp  5    MMA issuer (one elected lane); owns the TMEM allocation
-// Pipelines (all mbarrier based): K ring x2 and V ring x2 (freed by tcgen05.commit of the MMA that
-// read them), S/P double buffer in TMEM so QK^T of tile j+1 overlaps the softmax of tile j, and a
-// lazy O rescale (only when a row's max grows by more than 2^8) so the correction rarely touches TMEM.
+// CTA = 256 query rows (two 128-row tiles, "stages" 0 and 1) of one (sequence, head); 12 warps:
+//   warps 0-3   softmax of stage 0 (TMEM lanes 32w..32w+31), correction and epilogue of that stage
+//   warps 4-7   same for stage 1
+//   warp  8     producer: TMA loads of Q0, Q1, K[j], V[j]; builds the per-tile bias vector
+//   warp  9     MMA issuer (one elected lane); owns the TMEM allocation
+//   warps 10-11 idle (they exist so that setmaxnreg can hand their registers to the softmax warps)
+// The two stages share every K/V tile (half the shared-memory traffic per FLOP of a one-tile CTA) and
+// alternate on the tensor pipe: while warpgroup s runs the softmax of tile j, the MMA warp runs
+// P V (j) and Q K^T (j+1) of the other stage. TMEM: S0 | S1 | O0 | O1 (4 x 128 columns); P aliases S.
+// Lazy O rescale (only when a row's max grows by more than 2^8) keeps the correction off the hot loop.
 #include <mutex>
 
 #include "attn.cuh"
@@ -29,20 +33,20 @@ namespace cram {
 
 namespace {
 
-constexpr int kBlockM = 128;
-constexpr int kBlockN = 128;
-constexpr int kThreads = 192;
+constexpr int kBlockM = 128;  // rows per query tile (= TMEM lanes)
+constexpr int kStages = 2;    // query tiles per CTA
+constexpr int kBlockN = 128;  // keys per K/V tile
+constexpr int kThreads = 384;
 constexpr int kTmemCols = 512;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
 
 struct Barriers {
-  uint64_t q_full;
+  uint64_t q_full[2];
   uint64_t k_full[2], k_empty[2];
   uint64_t v_full[2], v_empty[2];
   uint64_t bias_full[2];
-  uint64_t s_full[2], p_full[2];
-  uint64_t o_done;
+  uint64_t s_full[2], p_full[2], o_done[2];  // indexed by query stage
 };
 
 template <int DH>
@@ -50,7 +54,7 @@ struct Smem {
   static constexpr int kTileBytes = kBlockN * DH * 2;  // one Q / K / V tile
   static constexpr int kSlabBytes = kBlockN * 128;     // 128 rows x 64 elements (one 128B swizzle slab)
   static constexpr int kQ = 0;
-  static constexpr int kK = kQ + kTileBytes;
+  static constexpr int kK = kQ + 2 * kTileBytes;
   static constexpr int kV = kK + 2 * kTileBytes;
   static constexpr int kBias = kV + 2 * kTileBytes;
   static constexpr int kBar = kBias + 2 * kBlockN * 4;
@@ -66,45 +70,187 @@ __device__ __forceinline__ float ex2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// packed fp32x2 arithmetic (FFMA2 / FADD2): two lanes per issue slot
+__device__ __forceinline__ uint64_t pk2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk2(uint64_t r, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(r));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t fmul2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+template <int N>
+__device__ __forceinline__ void setmaxnreg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
+}
+template <int N>
+__device__ __forceinline__ void setmaxnreg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
+}
 
 template <typename T>
 __device__ __forceinline__ uint32_t pack2(float lo, float hi);
 template <>
 __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float lo, float hi) {
-  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
-  return *reinterpret_cast<uint32_t*>(&v);
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
 }
 template <>
 __device__ __forceinline__ uint32_t pack2<__half>(float lo, float hi) {
-  __half2 v = __floats2half2_rn(lo, hi);
-  return *reinterpret_cast<uint32_t*>(&v);
+  uint32_t r;
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
+// One K/V tile of one query row (= one thread): S from TMEM -> t = S*scale2 + bias[k] -> running max
+// (lazy rescale of O) -> P = 2^(t - m) packed to T and written back over the S columns.
+// kDiag: the tile straddles the causal diagonal, columns > climit are masked.
+template <typename T, int DH, bool kDiag>
+__device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32_t o_addr, const float* __restrict__ bias,
+                                             const float scale2, const int climit, const bool first,
+                                             uint64_t* o_done_bar, const uint32_t o_done_parity, float& m_ref,
+                                             float& l) {
+  uint32_t s[4][32];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) ptx::tmem_ld32(s_addr + c * 32, s[c]);
+  ptx::tc_wait_ld();
+
+  const uint64_t sc2 = pk2(scale2, scale2);
+  const ulonglong2* b2 = reinterpret_cast<const ulonglong2*>(bias);
+  float mxa = -INFINITY, mxb = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      const ulonglong2 b = b2[c * 8 + i / 4];
+      const uint64_t t01 = ffma2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), sc2, b.x);
+      const uint64_t t23 = ffma2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), sc2, b.y);
+      float t0, t1, t2, t3;
+      upk2(t01, t0, t1);
+      upk2(t23, t2, t3);
+      if (kDiag) {
+        const int col = c * 32 + i;
+        t0 = (col + 0 <= climit) ? t0 : -INFINITY;
+        t1 = (col + 1 <= climit) ? t1 : -INFINITY;
+        t2 = (col + 2 <= climit) ? t2 : -INFINITY;
+        t3 = (col + 3 <= climit) ? t3 : -INFINITY;
+      }
+      s[c][i + 0] = __float_as_uint(t0);
+      s[c][i + 1] = __float_as_uint(t1);
+      s[c][i + 2] = __float_as_uint(t2);
+      s[c][i + 3] = __float_as_uint(t3);
+      mxa = fmax3(mxa, t0, t1);
+      mxb = fmax3(mxb, t2, t3);
+    }
+  }
+  const float mx = fmaxf(mxa, mxb);
+
+  // lazy rescale: move the reference max only when this tile beats it by more than 2^8
+  const bool need = mx > m_ref + kRescaleThreshold;
+  const float m_new = need ? mx : m_ref;
+  if (!first && __any_sync(0xffffffffu, need)) {
+    const float f = need ? ex2(m_ref - m_new) : 1.0f;  // m_ref = -inf gives 0
+    ptx::mbar_wait(o_done_bar, o_done_parity);         // P V of the previous tile has landed in O
+    ptx::tc_fence_after();
+    const uint64_t f2 = pk2(f, f);
+#pragma unroll
+    for (int c = 0; c < DH / 32; ++c) {
+      uint32_t o[32];
+      ptx::tmem_ld32(o_addr + c * 32, o);
+      ptx::tc_wait_ld();
+#pragma unroll
+      for (int i = 0; i < 32; i += 2) {
+        float a, b;
+        upk2(fmul2(pk2(__uint_as_float(o[i]), __uint_as_float(o[i + 1])), f2), a, b);
+        o[i] = __float_as_uint(a);
+        o[i + 1] = __float_as_uint(b);
+      }
+      ptx::tmem_st32(o_addr + c * 32, o);
+    }
+    l *= f;
+  }
+  m_ref = m_new;
+  const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
+  const uint64_t negm = pk2(-m_use, -m_use);
+
+  uint64_t la = pk2(0.f, 0.f), lb = pk2(0.f, 0.f);
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    uint32_t pk[32];
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+      const int c = half * 2 + cc;
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        float e0, e1, e2, e3;
+        upk2(fadd2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), negm), e0, e1);
+        upk2(fadd2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), negm), e2, e3);
+        const float p0 = ex2(e0), p1 = ex2(e1), p2 = ex2(e2), p3 = ex2(e3);
+        la = fadd2(la, pk2(p0, p1));
+        lb = fadd2(lb, pk2(p2, p3));
+        pk[cc * 16 + i / 2 + 0] = pack2<T>(p0, p1);
+        pk[cc * 16 + i / 2 + 1] = pack2<T>(p2, p3);
+      }
+    }
+    ptx::tmem_st32(s_addr + half * 32, pk);  // P over the S columns: 64 keys -> 32 packed columns
+  }
+  float l0, l1, l2, l3;
+  upk2(la, l0, l1);
+  upk2(lb, l2, l3);
+  l += (l0 + l1) + (l2 + l3);
 }
 
 template <typename T, int DH>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                           const __grid_constant__ CUtensorMap tmap_v, const cram_attn_prefill_params p,
-                          const int num_m_tiles) {
+                          const int num_pairs) {
   using S = Smem<DH>;
   constexpr int kSlabs = DH / 64;
   constexpr uint32_t kAbFmt = DType<T>::code == CRAM_BF16 ? 1u : 0u;
   constexpr uint32_t kIdescQK = ptx::umma_idesc_f16(kAbFmt, kBlockM, kBlockN, 0);
   constexpr uint32_t kIdescPV = ptx::umma_idesc_f16(kAbFmt, kBlockM, DH, 1);
 
-  // ---- which tile ------------------------------------------------------------------------------
+  // ---- which tile pair ---------------------------------------------------------------------------
   const int head = blockIdx.x % p.n_heads;
   const int rest = blockIdx.x / p.n_heads;
   const int seq = rest % p.n_seq;
-  const int m_tile = num_m_tiles - 1 - rest / p.n_seq;  // heaviest (latest) query tiles first
+  const int pair = num_pairs - 1 - rest / p.n_seq;  // heaviest (latest) query rows first
   const int q0 = p.cu_seqlens_q[seq], len_q = p.cu_seqlens_q[seq + 1] - q0;
-  if (m_tile * kBlockM >= len_q) return;
+  if (pair * kStages * kBlockM >= len_q) return;
   const int32_t* cuk = p.cu_seqlens_k ? p.cu_seqlens_k : p.cu_seqlens_q;
   const int k0 = cuk[seq], len_k = cuk[seq + 1] - k0;
   const int diag = len_k - len_q;  // query i sees keys <= i + diag
   const int kv_head = head / (p.n_heads / p.n_kv_heads);
-  int kv_end = len_k;
-  if (p.causal) kv_end = min(len_k, m_tile * kBlockM + kBlockM + diag);
-  const int n_tiles = kv_end > 0 ? (kv_end + kBlockN - 1) / kBlockN : 0;
+  auto tiles_of = [&](int s) {
+    const int mt = pair * kStages + s;
+    int kv_end = len_k;
+    if (p.causal) kv_end = min(len_k, mt * kBlockM + kBlockM + diag);
+    return (mt * kBlockM < len_q && kv_end > 0) ? (kv_end + kBlockN - 1) / kBlockN : 0;
+  };
+  const int n_t0 = tiles_of(0), n_t1 = tiles_of(1);
+  const int n_max = max(n_t0, n_t1);
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -114,54 +260,58 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  if (warp == 4 && lane == 0) {
+  if (warp == 8 && lane == 0) {
     ptx::prefetch_tmap(&tmap_q);
     ptx::prefetch_tmap(&tmap_k);
     ptx::prefetch_tmap(&tmap_v);
-    ptx::mbar_init(&bar->q_full, 1);
     for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&bar->q_full[i], 1);
       ptx::mbar_init(&bar->k_full[i], 1);
       ptx::mbar_init(&bar->k_empty[i], 1);
       ptx::mbar_init(&bar->v_full[i], 1);
       ptx::mbar_init(&bar->v_empty[i], 1);
       ptx::mbar_init(&bar->bias_full[i], 1);
       ptx::mbar_init(&bar->s_full[i], 1);
-      ptx::mbar_init(&bar->p_full[i], 128);
+      ptx::mbar_init(&bar->p_full[i], kBlockM);
+      ptx::mbar_init(&bar->o_done[i], 1);
     }
-    ptx::mbar_init(&bar->o_done, 1);
     ptx::fence_mbar_init();
   }
-  if (warp == 5) ptx::tmem_alloc(tmem_ptr_smem, kTmemCols);
+  if (warp == 9) ptx::tmem_alloc(tmem_ptr_smem, kTmemCols);
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
-  const uint32_t tmem_o = tmem_base + 2 * kBlockN;
 
-  if (warp == 4) {
-    // ============================== producer ====================================================
-    if (n_tiles > 0) {
+  if (warp >= 8) {
+    setmaxnreg_dec<56>();
+    if (warp == 8) {
+      // ============================== producer ==================================================
       const bool biased = p.logcred != nullptr && ((p.head_mask >> head) & 1ull);
       const int bias_len = p.bias_len ? p.bias_len[seq] : len_k;
       if (lane == 0) {
-        ptx::mbar_expect_tx(&bar->q_full, S::kTileBytes);
 #pragma unroll
-        for (int s = 0; s < kSlabs; ++s)
-          ptx::tma_load_2d(smem + S::kQ + s * S::kSlabBytes, &tmap_q, &bar->q_full, head * DH + s * 64,
-                           q0 + m_tile * kBlockM);
+        for (int s = 0; s < kStages; ++s) {
+          if ((s ? n_t1 : n_t0) == 0) continue;
+          ptx::mbar_expect_tx(&bar->q_full[s], S::kTileBytes);
+#pragma unroll
+          for (int sl = 0; sl < kSlabs; ++sl)
+            ptx::tma_load_2d(smem + S::kQ + s * S::kTileBytes + sl * S::kSlabBytes, &tmap_q, &bar->q_full[s],
+                             head * DH + sl * 64, q0 + (pair * kStages + s) * kBlockM);
+        }
       }
-      for (int j = 0; j < n_tiles; ++j) {
+      for (int j = 0; j < n_max; ++j) {
         const int st = j & 1;
         const uint32_t ph = (j >> 1) & 1;
         if (lane == 0) {
           ptx::mbar_wait(&bar->k_empty[st], ph ^ 1);
           ptx::mbar_expect_tx(&bar->k_full[st], S::kTileBytes);
 #pragma unroll
-          for (int s = 0; s < kSlabs; ++s)
-            ptx::tma_load_2d(smem + S::kK + st * S::kTileBytes + s * S::kSlabBytes, &tmap_k, &bar->k_full[st],
-                             kv_head * DH + s * 64, k0 + j * kBlockN);
+          for (int sl = 0; sl < kSlabs; ++sl)
+            ptx::tma_load_2d(smem + S::kK + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_k, &bar->k_full[st],
+                             kv_head * DH + sl * 64, k0 + j * kBlockN);
         }
-        // V slot and bias slot st are free once P[j-2] V[j-2] has completed.
+        // V slot and bias slot st are free once every P V of tile j-2 has completed.
         ptx::mbar_wait(&bar->v_empty[st], ph ^ 1);
         {
           float4 b4;
@@ -181,163 +331,103 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
           ptx::mbar_arrive(&bar->bias_full[st]);
           ptx::mbar_expect_tx(&bar->v_full[st], S::kTileBytes);
 #pragma unroll
-          for (int s = 0; s < kSlabs; ++s)
-            ptx::tma_load_2d(smem + S::kV + st * S::kTileBytes + s * S::kSlabBytes, &tmap_v, &bar->v_full[st],
-                             kv_head * DH + s * 64, k0 + j * kBlockN);
+          for (int sl = 0; sl < kSlabs; ++sl)
+            ptx::tma_load_2d(smem + S::kV + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_v, &bar->v_full[st],
+                             kv_head * DH + sl * 64, k0 + j * kBlockN);
         }
       }
-    }
-  } else if (warp == 5) {
-    // ============================== MMA issuer ==================================================
-    if (lane == 0 && n_tiles > 0) {
+    } else if (warp == 9 && lane == 0) {
+      // ============================== MMA issuer ================================================
       const uint32_t q_addr = ptx::smem_u32(smem + S::kQ);
       const uint32_t k_addr = ptx::smem_u32(smem + S::kK);
       const uint32_t v_addr = ptx::smem_u32(smem + S::kV);
-      auto issue_qk = [&](int j) {
+      // S[s] = Q[s] K[j]^T. Issued right after P[s] V[j-1]: the tensor pipe executes in order, so the
+      // overwrite of the aliased P columns cannot pass the read of P.
+      auto issue_qk = [&](int s, int j) {
         const int st = j & 1;
         ptx::mbar_wait(&bar->k_full[st], (j >> 1) & 1);
         ptx::tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < DH / 16; ++kk) {
           const uint32_t off = (kk >> 2) * S::kSlabBytes + (kk & 3) * 32;
-          ptx::mma_ss(tmem_base + st * kBlockN, ptx::umma_desc_sw128(q_addr + off, 16, 1024),
+          ptx::mma_ss(tmem_base + s * kBlockN, ptx::umma_desc_sw128(q_addr + s * S::kTileBytes + off, 16, 1024),
                       ptx::umma_desc_sw128(k_addr + st * S::kTileBytes + off, 16, 1024), kIdescQK, kk > 0);
         }
-        ptx::tc_commit(&bar->k_empty[st]);
-        ptx::tc_commit(&bar->s_full[st]);
+        ptx::tc_commit(&bar->s_full[s]);
+        if (s == 1 || j >= n_t1) ptx::tc_commit(&bar->k_empty[st]);  // last stage to read K[j]
       };
-      ptx::mbar_wait(&bar->q_full, 0);
-      issue_qk(0);
-      for (int j = 0; j < n_tiles; ++j) {
+#pragma unroll
+      for (int s = 0; s < kStages; ++s) {
+        if ((s ? n_t1 : n_t0) > 0) {
+          ptx::mbar_wait(&bar->q_full[s], 0);
+          issue_qk(s, 0);
+        }
+      }
+      for (int j = 0; j < n_max; ++j) {
         const int st = j & 1;
         const uint32_t ph = (j >> 1) & 1;
-        if (j + 1 < n_tiles) issue_qk(j + 1);
-        ptx::mbar_wait(&bar->p_full[st], ph);
-        ptx::mbar_wait(&bar->v_full[st], ph);
-        ptx::tc_fence_after();
 #pragma unroll
-        for (int kk = 0; kk < kBlockN / 16; ++kk) {
-          ptx::mma_ts(tmem_o, tmem_base + st * kBlockN + kk * 8,
-                      ptx::umma_desc_sw128(v_addr + st * S::kTileBytes + kk * 2048, S::kSlabBytes, 1024), kIdescPV,
-                      (j > 0 || kk > 0) ? 1u : 0u);
+        for (int s = 0; s < kStages; ++s) {
+          if (j >= (s ? n_t1 : n_t0)) continue;
+          ptx::mbar_wait(&bar->v_full[st], ph);
+          ptx::mbar_wait(&bar->p_full[s], j & 1);
+          ptx::tc_fence_after();
+          const uint32_t tmem_o = tmem_base + 2 * kBlockN + s * kBlockN;
+#pragma unroll
+          for (int kk = 0; kk < kBlockN / 16; ++kk) {
+            ptx::mma_ts(tmem_o, tmem_base + s * kBlockN + kk * 8,
+                        ptx::umma_desc_sw128(v_addr + st * S::kTileBytes + kk * 2048, S::kSlabBytes, 1024), kIdescPV,
+                        (j > 0 || kk > 0) ? 1u : 0u);
+          }
+          ptx::tc_commit(&bar->o_done[s]);
+          if (s == 1 || j >= n_t1) ptx::tc_commit(&bar->v_empty[st]);  // last stage to read V[j]
+          if (j + 1 < (s ? n_t1 : n_t0)) issue_qk(s, j + 1);
         }
-        ptx::tc_commit(&bar->v_empty[st]);
-        ptx::tc_commit(&bar->o_done);
       }
     }
   } else {
     // ============================== softmax / correction / epilogue ================================
-    const int row = warp * 32 + lane;             // row inside the tile == TMEM lane
-    const int qrow = m_tile * kBlockM + row;      // row inside the sequence
-    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
+    setmaxnreg_inc<224>();
+    const int s = warp >> 2;                      // query stage of this warpgroup
+    const int row = (warp & 3) * 32 + lane;       // row inside the tile == TMEM lane
+    const int mt = pair * kStages + s;
+    const int qrow = mt * kBlockM + row;          // row inside the sequence
+    const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t s_addr = tmem_base + lane_off + s * kBlockN;
+    const uint32_t o_addr = tmem_base + lane_off + 2 * kBlockN + s * kBlockN;
     const float scale2 = p.scale * kLog2e;
+    const int nt = s ? n_t1 : n_t0;
     float m_ref = -INFINITY, l = 0.f;
 
-    for (int j = 0; j < n_tiles; ++j) {
+    for (int j = 0; j < nt; ++j) {
       const int st = j & 1;
-      const uint32_t ph = (j >> 1) & 1;
-      ptx::mbar_wait(&bar->bias_full[st], ph);
-      ptx::mbar_wait(&bar->s_full[st], ph);
+      ptx::mbar_wait(&bar->bias_full[st], (j >> 1) & 1);
+      ptx::mbar_wait(&bar->s_full[s], j & 1);
       ptx::tc_fence_after();
-      uint32_t s[4][32];
-      const uint32_t s_addr = tmem_base + lane_off + st * kBlockN;
-#pragma unroll
-      for (int c = 0; c < 4; ++c) ptx::tmem_ld32(s_addr + c * 32, s[c]);
-      ptx::tc_wait_ld();
-
-      const float4* bias4 = reinterpret_cast<const float4*>(s_bias + st * kBlockN);
-      const bool diag_tile = p.causal && (j * kBlockN + kBlockN - 1 > m_tile * kBlockM + diag);
+      const bool diag_tile = p.causal && (j * kBlockN + kBlockN - 1 > mt * kBlockM + diag);
       const int climit = qrow + diag - j * kBlockN;  // columns <= climit are visible
-      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-#pragma unroll
-        for (int i = 0; i < 32; i += 4) {
-          const float4 b = bias4[c * 8 + i / 4];
-          float t0 = fmaf(__uint_as_float(s[c][i + 0]), scale2, b.x);
-          float t1 = fmaf(__uint_as_float(s[c][i + 1]), scale2, b.y);
-          float t2 = fmaf(__uint_as_float(s[c][i + 2]), scale2, b.z);
-          float t3 = fmaf(__uint_as_float(s[c][i + 3]), scale2, b.w);
-          if (diag_tile) {
-            const int col = c * 32 + i;
-            t0 = (col + 0 <= climit) ? t0 : -INFINITY;
-            t1 = (col + 1 <= climit) ? t1 : -INFINITY;
-            t2 = (col + 2 <= climit) ? t2 : -INFINITY;
-            t3 = (col + 3 <= climit) ? t3 : -INFINITY;
-          }
-          s[c][i + 0] = __float_as_uint(t0);
-          s[c][i + 1] = __float_as_uint(t1);
-          s[c][i + 2] = __float_as_uint(t2);
-          s[c][i + 3] = __float_as_uint(t3);
-          mx0 = fmaxf(mx0, t0);
-          mx1 = fmaxf(mx1, t1);
-          mx2 = fmaxf(mx2, t2);
-          mx3 = fmaxf(mx3, t3);
-        }
-      }
-      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-
-      // lazy rescale: move the reference max only when this tile beats it by more than 2^8
-      const bool need = mx > m_ref + kRescaleThreshold;
-      const float m_new = need ? mx : m_ref;
-      if (j > 0 && __any_sync(0xffffffffu, need)) {
-        const float f = need ? ex2(m_ref - m_new) : 1.0f;  // m_ref = -inf gives 0
-        ptx::mbar_wait(&bar->o_done, (j - 1) & 1);         // P[j-1] V[j-1] has landed in O
-        ptx::tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < DH / 32; ++c) {
-          uint32_t o[32];
-          ptx::tmem_ld32(tmem_o + lane_off + c * 32, o);
-          ptx::tc_wait_ld();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * f);
-          ptx::tmem_st32(tmem_o + lane_off + c * 32, o);
-        }
-        l *= f;
-      }
-      m_ref = m_new;
-      const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
-
-      float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        uint32_t pk[32];
-#pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-          const int c = half * 2 + cc;
-#pragma unroll
-          for (int i = 0; i < 32; i += 4) {
-            const float p0 = ex2(__uint_as_float(s[c][i + 0]) - m_use);
-            const float p1 = ex2(__uint_as_float(s[c][i + 1]) - m_use);
-            const float p2 = ex2(__uint_as_float(s[c][i + 2]) - m_use);
-            const float p3 = ex2(__uint_as_float(s[c][i + 3]) - m_use);
-            l0 += p0;
-            l1 += p1;
-            l2 += p2;
-            l3 += p3;
-            pk[cc * 16 + i / 2 + 0] = pack2<T>(p0, p1);
-            pk[cc * 16 + i / 2 + 1] = pack2<T>(p2, p3);
-          }
-        }
-        ptx::tmem_st32(s_addr + half * 32, pk);  // P over the S columns: 64 keys -> 32 packed columns
-      }
-      l += (l0 + l1) + (l2 + l3);
+      if (diag_tile)
+        softmax_tile<T, DH, true>(s_addr, o_addr, s_bias + st * kBlockN, scale2, climit, j == 0, &bar->o_done[s],
+                                  (j - 1) & 1, m_ref, l);
+      else
+        softmax_tile<T, DH, false>(s_addr, o_addr, s_bias + st * kBlockN, scale2, climit, j == 0, &bar->o_done[s],
+                                   (j - 1) & 1, m_ref, l);
       ptx::tc_wait_st();
       ptx::tc_fence_before();
-      ptx::mbar_arrive(&bar->p_full[st]);
+      ptx::mbar_arrive(&bar->p_full[s]);
     }
 
     // ---- epilogue: O / l -> global ---------------------------------------------------------------
     const bool row_ok = qrow < len_q;
     T* out = reinterpret_cast<T*>(p.out) + (int64_t)(q0 + qrow) * p.out_row_stride + (int64_t)head * DH;
-    if (n_tiles > 0) {
-      ptx::mbar_wait(&bar->o_done, (n_tiles - 1) & 1);
+    if (nt > 0) {
+      ptx::mbar_wait(&bar->o_done[s], (nt - 1) & 1);
       ptx::tc_fence_after();
       const float inv = l > 0.f ? 1.0f / l : 0.f;
 #pragma unroll
       for (int c = 0; c < DH / 32; ++c) {
         uint32_t o[32];
-        ptx::tmem_ld32(tmem_o + lane_off + c * 32, o);
+        ptx::tmem_ld32(o_addr + c * 32, o);
         ptx::tc_wait_ld();
         if (row_ok) {
 #pragma unroll
@@ -362,7 +452,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
 
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 5) ptx::tmem_dealloc(tmem_base, kTmemCols);
+  if (warp == 9) ptx::tmem_dealloc(tmem_base, kTmemCols);
 }
 
 // ---- host side -----------------------------------------------------------------------------------
@@ -412,8 +502,8 @@ int launch_t(const cram_attn_prefill_params& p, cudaStream_t stream) {
   if ((rc = make_tmap(&tq, p.q, p.dtype, (int64_t)p.n_heads * DH, p.total_q, p.q_row_stride)) != CRAM_OK) return rc;
   if ((rc = make_tmap(&tk, p.k, p.dtype, (int64_t)p.n_kv_heads * DH, p.total_k, p.k_row_stride)) != CRAM_OK) return rc;
   if ((rc = make_tmap(&tv, p.v, p.dtype, (int64_t)p.n_kv_heads * DH, p.total_k, p.v_row_stride)) != CRAM_OK) return rc;
-  const int num_m_tiles = (p.max_seqlen_q + kBlockM - 1) / kBlockM;
-  const long long grid = (long long)num_m_tiles * p.n_seq * p.n_heads;
+  const int num_pairs = (p.max_seqlen_q + kStages * kBlockM - 1) / (kStages * kBlockM);
+  const long long grid = (long long)num_pairs * p.n_seq * p.n_heads;
   if (grid == 0) return CRAM_OK;
   CRAM_REQUIRE(grid < (1ll << 31), "cram_attn_prefill: grid too large");
   auto kern = attn_prefill_sm100_kernel<T, DH>;
@@ -422,7 +512,7 @@ int launch_t(const cram_attn_prefill_params& p, cudaStream_t stream) {
     CRAM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<DH>::kRequest));
     attr_set = true;
   }
-  kern<<<(unsigned)grid, kThreads, Smem<DH>::kRequest, stream>>>(tq, tk, tv, p, num_m_tiles);
+  kern<<<(unsigned)grid, kThreads, Smem<DH>::kRequest, stream>>>(tq, tk, tv, p, num_pairs);
   return check_launch("attn_prefill_sm100_kernel");
 }
 
