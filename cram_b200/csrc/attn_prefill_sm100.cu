@@ -25,6 +25,7 @@
 // P V (j) and Q K^T (j+1) of the other stage. TMEM: S0 | S1 | O0 | O1 (4 x 128 columns); P aliases S.
 // Lazy O rescale (only when a row's max grows by more than 2^8) keeps the correction off the hot loop.
 #include <mutex>
+#include <utility>
 
 #include "attn.cuh"
 #include "sm100_ptx.cuh"
@@ -127,25 +128,26 @@ __device__ __forceinline__ uint32_t pack2<__half>(float lo, float hi) {
 // (lazy rescale of O) -> P = 2^(t - m) packed to T and written back over the S columns.
 // kDiag: the tile straddles the causal diagonal, columns > climit are masked.
 template <typename T, int DH, bool kDiag>
-__device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32_t o_addr, const float* __restrict__ bias,
+__device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32_t o_addr, const uint32_t bias,
                                              const float scale2, const int climit, const bool first,
                                              uint64_t* o_done_bar, const uint32_t o_done_parity, float& m_ref,
                                              float& l) {
   uint32_t s[4][32];
-#pragma unroll
-  for (int c = 0; c < 4; ++c) ptx::tmem_ld32(s_addr + c * 32, s[c]);
-  ptx::tc_wait_ld();
-
   const uint64_t sc2 = pk2(scale2, scale2);
-  const ulonglong2* b2 = reinterpret_cast<const ulonglong2*>(bias);
-  float mxa = -INFINITY, mxb = -INFINITY;
+  float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+  // TMEM -> registers in four 32-column chunks; the load of chunk c+1 is in flight while chunk c gets
+  // its bias FFMA2 and running max.
+  ptx::tmem_ld32(s_addr, s[0]);
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
+    ptx::tc_wait_ld_regs(s[c]);
+    if (c + 1 < 4) ptx::tmem_ld32(s_addr + (c + 1) * 32, s[c + 1]);
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
-      const ulonglong2 b = b2[c * 8 + i / 4];
-      const uint64_t t01 = ffma2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), sc2, b.x);
-      const uint64_t t23 = ffma2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), sc2, b.y);
+      uint64_t bx, by;
+      asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(bx), "=l"(by) : "r"(bias + (c * 32 + i) * 4));
+      const uint64_t t01 = ffma2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), sc2, bx);
+      const uint64_t t23 = ffma2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), sc2, by);
       float t0, t1, t2, t3;
       upk2(t01, t0, t1);
       upk2(t23, t2, t3);
@@ -160,10 +162,16 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
       s[c][i + 1] = __float_as_uint(t1);
       s[c][i + 2] = __float_as_uint(t2);
       s[c][i + 3] = __float_as_uint(t3);
-      mxa = fmax3(mxa, t0, t1);
-      mxb = fmax3(mxb, t2, t3);
+      if (i & 4) {
+        mx2 = fmax3(mx2, t0, t1);
+        mx3 = fmax3(mx3, t2, t3);
+      } else {
+        mx0 = fmax3(mx0, t0, t1);
+        mx1 = fmax3(mx1, t2, t3);
+      }
     }
   }
+  const float mxa = fmaxf(mx0, mx1), mxb = fmaxf(mx2, mx3);
   const float mx = fmaxf(mxa, mxb);
 
   // lazy rescale: move the reference max only when this tile beats it by more than 2^8
@@ -219,6 +227,24 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
   upk2(la, l0, l1);
   upk2(lb, l2, l3);
   l += (l0 + l1) + (l2 + l3);
+}
+
+// ---- MMA issue helpers (compile-time K steps; see ptx::mma_ss_imm) ---------------------------------
+constexpr uint32_t kDescHi = ptx::umma_desc_hi(1024);  // SBO = 8 rows x 128 B, version 1, SWIZZLE_128B
+// byte offset (>> 4) of K-step kk inside a K-major 128B-swizzled [128 x DH] tile
+constexpr int kmajor_off16(int kk) { return ((kk >> 2) * (kBlockN * 128) + (kk & 3) * 32) >> 4; }
+
+template <int... KK>
+__device__ __forceinline__ void issue_qk_steps(uint32_t d_tmem, uint32_t q_lo, uint32_t k_lo, uint32_t idesc,
+                                               std::integer_sequence<int, KK...>) {
+  (ptx::mma_ss_imm<kDescHi, 0, kmajor_off16(KK), kmajor_off16(KK)>(d_tmem, q_lo, k_lo, idesc, KK > 0 ? 1u : 0u), ...);
+}
+// O += P V for key steps KK (16 keys each): P step kk sits at TMEM column offset 8*kk (packed 16-bit),
+// V step kk 16 rows x 128 B further down the MN-major tile.
+template <int... KK>
+__device__ __forceinline__ void issue_pv_steps(uint32_t o_tmem, uint32_t p_tmem, uint32_t v_lo, uint32_t idesc,
+                                               bool acc_first, std::integer_sequence<int, KK...>) {
+  (ptx::mma_ts_imm<kDescHi, 0, KK * 8, KK * 128>(o_tmem, p_tmem, v_lo, idesc, (acc_first || KK > 0) ? 1u : 0u), ...);
 }
 
 template <typename T, int DH>
@@ -338,21 +364,18 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       }
     } else if (warp == 9 && lane == 0) {
       // ============================== MMA issuer ================================================
-      const uint32_t q_addr = ptx::smem_u32(smem + S::kQ);
-      const uint32_t k_addr = ptx::smem_u32(smem + S::kK);
-      const uint32_t v_addr = ptx::smem_u32(smem + S::kV);
+      const uint32_t q_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + S::kQ), 16);
+      const uint32_t k_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + S::kK), 16);
+      const uint32_t v_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + S::kV), S::kSlabBytes);
+      constexpr uint32_t kTile16 = S::kTileBytes >> 4;
       // S[s] = Q[s] K[j]^T. Issued right after P[s] V[j-1]: the tensor pipe executes in order, so the
       // overwrite of the aliased P columns cannot pass the read of P.
       auto issue_qk = [&](int s, int j) {
         const int st = j & 1;
         ptx::mbar_wait(&bar->k_full[st], (j >> 1) & 1);
         ptx::tc_fence_after();
-#pragma unroll
-        for (int kk = 0; kk < DH / 16; ++kk) {
-          const uint32_t off = (kk >> 2) * S::kSlabBytes + (kk & 3) * 32;
-          ptx::mma_ss(tmem_base + s * kBlockN, ptx::umma_desc_sw128(q_addr + s * S::kTileBytes + off, 16, 1024),
-                      ptx::umma_desc_sw128(k_addr + st * S::kTileBytes + off, 16, 1024), kIdescQK, kk > 0);
-        }
+        issue_qk_steps(tmem_base + s * kBlockN, q_lo + s * kTile16, k_lo + st * kTile16, kIdescQK,
+                       std::make_integer_sequence<int, DH / 16>{});
         ptx::tc_commit(&bar->s_full[s]);
         if (s == 1 || j >= n_t1) ptx::tc_commit(&bar->k_empty[st]);  // last stage to read K[j]
       };
@@ -372,13 +395,8 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
           ptx::mbar_wait(&bar->v_full[st], ph);
           ptx::mbar_wait(&bar->p_full[s], j & 1);
           ptx::tc_fence_after();
-          const uint32_t tmem_o = tmem_base + 2 * kBlockN + s * kBlockN;
-#pragma unroll
-          for (int kk = 0; kk < kBlockN / 16; ++kk) {
-            ptx::mma_ts(tmem_o, tmem_base + s * kBlockN + kk * 8,
-                        ptx::umma_desc_sw128(v_addr + st * S::kTileBytes + kk * 2048, S::kSlabBytes, 1024), kIdescPV,
-                        (j > 0 || kk > 0) ? 1u : 0u);
-          }
+          issue_pv_steps(tmem_base + 2 * kBlockN + s * kBlockN, tmem_base + s * kBlockN, v_lo + st * kTile16, kIdescPV,
+                         j > 0, std::make_integer_sequence<int, kBlockN / 16>{});
           ptx::tc_commit(&bar->o_done[s]);
           if (s == 1 || j >= n_t1) ptx::tc_commit(&bar->v_empty[st]);  // last stage to read V[j]
           if (j + 1 < (s ? n_t1 : n_t0)) issue_qk(s, j + 1);
@@ -396,6 +414,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     const uint32_t s_addr = tmem_base + lane_off + s * kBlockN;
     const uint32_t o_addr = tmem_base + lane_off + 2 * kBlockN + s * kBlockN;
     const float scale2 = p.scale * kLog2e;
+    const uint32_t bias_addr = ptx::smem_u32(s_bias);
     const int nt = s ? n_t1 : n_t0;
     float m_ref = -INFINITY, l = 0.f;
 
@@ -407,10 +426,10 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       const bool diag_tile = p.causal && (j * kBlockN + kBlockN - 1 > mt * kBlockM + diag);
       const int climit = qrow + diag - j * kBlockN;  // columns <= climit are visible
       if (diag_tile)
-        softmax_tile<T, DH, true>(s_addr, o_addr, s_bias + st * kBlockN, scale2, climit, j == 0, &bar->o_done[s],
+        softmax_tile<T, DH, true>(s_addr, o_addr, bias_addr + st * kBlockN * 4, scale2, climit, j == 0, &bar->o_done[s],
                                   (j - 1) & 1, m_ref, l);
       else
-        softmax_tile<T, DH, false>(s_addr, o_addr, s_bias + st * kBlockN, scale2, climit, j == 0, &bar->o_done[s],
+        softmax_tile<T, DH, false>(s_addr, o_addr, bias_addr + st * kBlockN * 4, scale2, climit, j == 0, &bar->o_done[s],
                                    (j - 1) & 1, m_ref, l);
       ptx::tc_wait_st();
       ptx::tc_fence_before();

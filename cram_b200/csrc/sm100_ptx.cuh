@@ -117,6 +117,56 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
       : "memory");
 }
 
+// tcgen05.wait::ld that names the registers of the chunk being waited for as in/out operands, so that
+// neither the compiler front end nor ptxas can move a use of them above the wait.
+__device__ __forceinline__ void tc_wait_ld_regs(uint32_t (&r)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                 "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                 "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]),
+                 "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]),
+                 "+r"(r[30]), "+r"(r[31])
+               :
+               : "memory");
+}
+
+// MMA issue with every per-instruction offset as an immediate inside the asm block: the descriptors'
+// low words (address field, 16-byte units) and the TMEM addresses are `base + constant`, computed next
+// to the instruction so nothing loop-invariant is hoisted into (and spilled from) the issuing lane.
+// D[tmem] (+)= A[smem desc] * B[smem desc]
+template <uint32_t kDescHi, int kDOff, int kAOff16, int kBOff16>
+__device__ __forceinline__ void mma_ss_imm(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t idesc,
+                                           uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b32 d, al, bl;\n\t.reg .b64 ad, bd;\n\t"
+      "add.u32 d, %0, %5;\n\tadd.u32 al, %1, %6;\n\tadd.u32 bl, %2, %7;\n\t"
+      "mov.b64 ad, {al, %8};\n\tmov.b64 bd, {bl, %8};\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [d], ad, bd, %3, p;\n\t}" ::"r"(d_tmem),
+      "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "n"(kDOff), "n"(kAOff16), "n"(kBOff16), "n"(kDescHi)
+      : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem desc]
+template <uint32_t kDescHi, int kDOff, int kAOff, int kBOff16>
+__device__ __forceinline__ void mma_ts_imm(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t idesc,
+                                           uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b32 d, a, bl;\n\t.reg .b64 bd;\n\t"
+      "add.u32 d, %0, %5;\n\tadd.u32 a, %1, %6;\n\tadd.u32 bl, %2, %7;\n\t"
+      "mov.b64 bd, {bl, %8};\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [d], [a], bd, %3, p;\n\t}" ::"r"(d_tmem),
+      "r"(a_tmem), "r"(b_lo), "r"(idesc), "r"(accumulate), "n"(kDOff), "n"(kAOff), "n"(kBOff16), "n"(kDescHi)
+      : "memory");
+}
+// low / high 32-bit words of a 128B-swizzle UMMA shared-memory descriptor
+__device__ __forceinline__ uint32_t umma_desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return ((smem_addr >> 4) & 0x3FFF) | (((lbo_bytes >> 4) & 0x3FFF) << 16);
+}
+__host__ __device__ constexpr uint32_t umma_desc_hi(uint32_t sbo_bytes) {
+  return ((sbo_bytes >> 4) & 0x3FFF) | (1u << 14) | (2u << 29);
+}
+
 // ---- UMMA descriptors (cute/arch/mma_sm100_desc.hpp bit layout) -----------------------------------
 // 128-byte-swizzled shared-memory operand. Addresses/offsets are in bytes, encoded >> 4.
 //   K-major  (Q, K tiles: rows = M/N, 64 contraction elements per 128-byte row):  LBO unused (1),
