@@ -36,7 +36,9 @@ namespace {
 
 constexpr int kBlockM = 128;  // rows per query tile (= TMEM lanes)
 constexpr int kStages = 2;    // query tiles per CTA
-constexpr int kBlockN = 128;  // keys per K/V tile
+constexpr int kBlockN = 64;   // keys per K/V tile
+constexpr int kKV = 4;        // K ring depth = V ring depth
+constexpr int kBiasRing = 8;  // bias vectors in flight (written with K[j], read until P V[j] is done)
 constexpr int kThreads = 384;
 constexpr int kTmemCols = 512;
 constexpr float kLog2e = 1.4426950408889634f;
@@ -44,21 +46,25 @@ constexpr float kRescaleThreshold = 8.0f;  // log2 units
 
 struct Barriers {
   uint64_t q_full[2];
-  uint64_t k_full[2], k_empty[2];
-  uint64_t v_full[2], v_empty[2];
-  uint64_t bias_full[2];
-  uint64_t s_full[2], p_full[2], o_done[2];  // indexed by query stage
+  uint64_t k_full[kKV], k_empty[kKV];
+  uint64_t v_full[kKV], v_empty[kKV];
+  uint64_t bias_full[kBiasRing];
+  uint64_t s_full[2][2], p_full[2][2];  // [query stage][S buffer]
+  uint64_t o_done[2];                   // [query stage] one phase per P V (lazy-rescale wait)
+  uint64_t o_final[2];                  // [query stage] single phase: the last P V has completed
 };
 
 template <int DH>
 struct Smem {
-  static constexpr int kTileBytes = kBlockN * DH * 2;  // one Q / K / V tile
-  static constexpr int kSlabBytes = kBlockN * 128;     // 128 rows x 64 elements (one 128B swizzle slab)
+  static constexpr int kQTileBytes = kBlockM * DH * 2;
+  static constexpr int kQSlabBytes = kBlockM * 128;  // 128 rows x 64 elements (one 128B swizzle slab)
+  static constexpr int kTileBytes = kBlockN * DH * 2;  // one K / V tile
+  static constexpr int kSlabBytes = kBlockN * 128;     // 64 rows x 64 elements
   static constexpr int kQ = 0;
-  static constexpr int kK = kQ + 2 * kTileBytes;
-  static constexpr int kV = kK + 2 * kTileBytes;
-  static constexpr int kBias = kV + 2 * kTileBytes;
-  static constexpr int kBar = kBias + 2 * kBlockN * 4;
+  static constexpr int kK = kQ + kStages * kQTileBytes;
+  static constexpr int kV = kK + kKV * kTileBytes;
+  static constexpr int kBias = kV + kKV * kTileBytes;
+  static constexpr int kBar = kBias + kBiasRing * kBlockN * 4;
   static constexpr int kTmemPtr = kBar + (int)sizeof(Barriers);
   static constexpr int kEnd = kTmemPtr + 16;
   // dynamic smem request: + 1024 for manual alignment; padded above half an SM so that exactly one
@@ -132,16 +138,16 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
                                              const float scale2, const int climit, const bool first,
                                              uint64_t* o_done_bar, const uint32_t o_done_parity, float& m_ref,
                                              float& l) {
-  uint32_t s[4][32];
+  uint32_t s[2][32];
   const uint64_t sc2 = pk2(scale2, scale2);
   float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-  // TMEM -> registers in four 32-column chunks; the load of chunk c+1 is in flight while chunk c gets
+  // TMEM -> registers in two 32-column chunks; the load of chunk c+1 is in flight while chunk c gets
   // its bias FFMA2 and running max.
   ptx::tmem_ld32(s_addr, s[0]);
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
+  for (int c = 0; c < 2; ++c) {
     ptx::tc_wait_ld_regs(s[c]);
-    if (c + 1 < 4) ptx::tmem_ld32(s_addr + (c + 1) * 32, s[c + 1]);
+    if (c + 1 < 2) ptx::tmem_ld32(s_addr + (c + 1) * 32, s[c + 1]);
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
       uint64_t bx, by;
@@ -203,26 +209,22 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
   const uint64_t negm = pk2(-m_use, -m_use);
 
   uint64_t la = pk2(0.f, 0.f), lb = pk2(0.f, 0.f);
+  uint32_t pk[32];
 #pragma unroll
-  for (int half = 0; half < 2; ++half) {
-    uint32_t pk[32];
+  for (int c = 0; c < 2; ++c) {
 #pragma unroll
-    for (int cc = 0; cc < 2; ++cc) {
-      const int c = half * 2 + cc;
-#pragma unroll
-      for (int i = 0; i < 32; i += 4) {
-        float e0, e1, e2, e3;
-        upk2(fadd2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), negm), e0, e1);
-        upk2(fadd2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), negm), e2, e3);
-        const float p0 = ex2(e0), p1 = ex2(e1), p2 = ex2(e2), p3 = ex2(e3);
-        la = fadd2(la, pk2(p0, p1));
-        lb = fadd2(lb, pk2(p2, p3));
-        pk[cc * 16 + i / 2 + 0] = pack2<T>(p0, p1);
-        pk[cc * 16 + i / 2 + 1] = pack2<T>(p2, p3);
-      }
+    for (int i = 0; i < 32; i += 4) {
+      float e0, e1, e2, e3;
+      upk2(fadd2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), negm), e0, e1);
+      upk2(fadd2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), negm), e2, e3);
+      const float p0 = ex2(e0), p1 = ex2(e1), p2 = ex2(e2), p3 = ex2(e3);
+      la = fadd2(la, pk2(p0, p1));
+      lb = fadd2(lb, pk2(p2, p3));
+      pk[c * 16 + i / 2 + 0] = pack2<T>(p0, p1);
+      pk[c * 16 + i / 2 + 1] = pack2<T>(p2, p3);
     }
-    ptx::tmem_st32(s_addr + half * 32, pk);  // P over the S columns: 64 keys -> 32 packed columns
   }
+  ptx::tmem_st32(s_addr, pk);  // P over the S columns: 64 keys -> 32 packed columns
   float l0, l1, l2, l3;
   upk2(la, l0, l1);
   upk2(lb, l2, l3);
@@ -232,12 +234,14 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
 // ---- MMA issue helpers (compile-time K steps; see ptx::mma_ss_imm) ---------------------------------
 constexpr uint32_t kDescHi = ptx::umma_desc_hi(1024);  // SBO = 8 rows x 128 B, version 1, SWIZZLE_128B
 // byte offset (>> 4) of K-step kk inside a K-major 128B-swizzled [128 x DH] tile
-constexpr int kmajor_off16(int kk) { return ((kk >> 2) * (kBlockN * 128) + (kk & 3) * 32) >> 4; }
+constexpr int kmajor_off16(int kk, int slab_bytes) { return ((kk >> 2) * slab_bytes + (kk & 3) * 32) >> 4; }
 
 template <int... KK>
 __device__ __forceinline__ void issue_qk_steps(uint32_t d_tmem, uint32_t q_lo, uint32_t k_lo, uint32_t idesc,
                                                std::integer_sequence<int, KK...>) {
-  (ptx::mma_ss_imm<kDescHi, 0, kmajor_off16(KK), kmajor_off16(KK)>(d_tmem, q_lo, k_lo, idesc, KK > 0 ? 1u : 0u), ...);
+  (ptx::mma_ss_imm<kDescHi, 0, kmajor_off16(KK, kBlockM * 128), kmajor_off16(KK, kBlockN * 128)>(d_tmem, q_lo, k_lo, idesc,
+                                                                                                    KK > 0 ? 1u : 0u),
+   ...);
 }
 // O += P V for key steps KK (16 keys each): P step kk sits at TMEM column offset 8*kk (packed 16-bit),
 // V step kk 16 rows x 128 B further down the MN-major tile.
@@ -269,7 +273,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
   const int k0 = cuk[seq], len_k = cuk[seq + 1] - k0;
   const int diag = len_k - len_q;  // query i sees keys <= i + diag
   const int kv_head = head / (p.n_heads / p.n_kv_heads);
-  auto tiles_of = [&](int s) {
+  auto tiles_of = [&](int s) {  // number of 64-key tiles query stage s visits
     const int mt = pair * kStages + s;
     int kv_end = len_k;
     if (p.causal) kv_end = min(len_k, mt * kBlockM + kBlockM + diag);
@@ -292,15 +296,20 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     ptx::prefetch_tmap(&tmap_v);
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&bar->q_full[i], 1);
+      ptx::mbar_init(&bar->o_done[i], 1);
+      ptx::mbar_init(&bar->o_final[i], 1);
+      for (int b = 0; b < 2; ++b) {
+        ptx::mbar_init(&bar->s_full[i][b], 1);
+        ptx::mbar_init(&bar->p_full[i][b], kBlockM);
+      }
+    }
+    for (int i = 0; i < kKV; ++i) {
       ptx::mbar_init(&bar->k_full[i], 1);
       ptx::mbar_init(&bar->k_empty[i], 1);
       ptx::mbar_init(&bar->v_full[i], 1);
       ptx::mbar_init(&bar->v_empty[i], 1);
-      ptx::mbar_init(&bar->bias_full[i], 1);
-      ptx::mbar_init(&bar->s_full[i], 1);
-      ptx::mbar_init(&bar->p_full[i], kBlockM);
-      ptx::mbar_init(&bar->o_done[i], 1);
     }
+    for (int i = 0; i < kBiasRing; ++i) ptx::mbar_init(&bar->bias_full[i], 1);
     ptx::fence_mbar_init();
   }
   if (warp == 9) ptx::tmem_alloc(tmem_ptr_smem, kTmemCols);
@@ -313,93 +322,106 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     setmaxnreg_dec<56>();
     if (warp == 8) {
       // ============================== producer ==================================================
+      // Order K[0], K[1], then per step t: K[t+2] (+ its bias vector), V[t] -- Q K^T runs two tiles
+      // ahead of P V. The bias vector of tile j lives until every P V[j] is done; the ring of 8 is
+      // safe because slot j&7 is rewritten only after the V slot of tile j-6 was seen free.
       const bool biased = p.logcred != nullptr && ((p.head_mask >> head) & 1ull);
       const int bias_len = p.bias_len ? p.bias_len[seq] : len_k;
       if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < kStages; ++s) {
           if ((s ? n_t1 : n_t0) == 0) continue;
-          ptx::mbar_expect_tx(&bar->q_full[s], S::kTileBytes);
+          ptx::mbar_expect_tx(&bar->q_full[s], S::kQTileBytes);
 #pragma unroll
           for (int sl = 0; sl < kSlabs; ++sl)
-            ptx::tma_load_2d(smem + S::kQ + s * S::kTileBytes + sl * S::kSlabBytes, &tmap_q, &bar->q_full[s],
+            ptx::tma_load_2d(smem + S::kQ + s * S::kQTileBytes + sl * S::kQSlabBytes, &tmap_q, &bar->q_full[s],
                              head * DH + sl * 64, q0 + (pair * kStages + s) * kBlockM);
         }
       }
-      for (int j = 0; j < n_max; ++j) {
-        const int st = j & 1;
-        const uint32_t ph = (j >> 1) & 1;
+      auto load_k_and_bias = [&](int j) {
+        const int st = j % kKV;
         if (lane == 0) {
-          ptx::mbar_wait(&bar->k_empty[st], ph ^ 1);
+          ptx::mbar_wait(&bar->k_empty[st], ((j / kKV) & 1) ^ 1);
           ptx::mbar_expect_tx(&bar->k_full[st], S::kTileBytes);
 #pragma unroll
           for (int sl = 0; sl < kSlabs; ++sl)
             ptx::tma_load_2d(smem + S::kK + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_k, &bar->k_full[st],
                              kv_head * DH + sl * 64, k0 + j * kBlockN);
         }
-        // V slot and bias slot st are free once every P V of tile j-2 has completed.
-        ptx::mbar_wait(&bar->v_empty[st], ph ^ 1);
         {
-          float4 b4;
-          float* bp = reinterpret_cast<float*>(&b4);
+          float2 b2;
+          float* bp = reinterpret_cast<float*>(&b2);
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int key = j * kBlockN + lane * 4 + e;
+          for (int e = 0; e < 2; ++e) {
+            const int key = j * kBlockN + lane * 2 + e;
             float v = 0.f;
             if (key >= len_k) v = -INFINITY;
             else if (biased && key < bias_len) v = load_logcred(p.logcred, (int64_t)k0 + key, p.logcred_dtype) * kLog2e;
             bp[e] = v;
           }
-          reinterpret_cast<float4*>(s_bias + st * kBlockN)[lane] = b4;
+          reinterpret_cast<float2*>(s_bias + (j % kBiasRing) * kBlockN)[lane] = b2;
         }
         __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&bar->bias_full[j % kBiasRing]);
+      };
+      if (n_max > 0) load_k_and_bias(0);
+      if (n_max > 1) load_k_and_bias(1);
+      for (int j = 0; j < n_max; ++j) {
+        if (j + 2 < n_max) load_k_and_bias(j + 2);
+        const int st = j % kKV;
         if (lane == 0) {
-          ptx::mbar_arrive(&bar->bias_full[st]);
+          ptx::mbar_wait(&bar->v_empty[st], ((j / kKV) & 1) ^ 1);
           ptx::mbar_expect_tx(&bar->v_full[st], S::kTileBytes);
 #pragma unroll
           for (int sl = 0; sl < kSlabs; ++sl)
             ptx::tma_load_2d(smem + S::kV + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_v, &bar->v_full[st],
                              kv_head * DH + sl * 64, k0 + j * kBlockN);
         }
+        __syncwarp();
       }
-    } else if (warp == 9 && lane == 0) {
+    } else if (warp == 9 && ptx::elect_one_sync()) {
       // ============================== MMA issuer ================================================
+      // Per query stage s the S accumulator is double-buffered (2 x 64 columns): Q K^T of tile j+2 goes
+      // into the buffer whose P (tile j) the P V just issued has consumed -- the tensor pipe executes in
+      // order -- so S of the next tile is always ready while the softmax warps work on the current one.
       const uint32_t q_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + S::kQ), 16);
       const uint32_t k_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + S::kK), 16);
       const uint32_t v_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + S::kV), S::kSlabBytes);
+      constexpr uint32_t kQTile16 = S::kQTileBytes >> 4;
       constexpr uint32_t kTile16 = S::kTileBytes >> 4;
-      // S[s] = Q[s] K[j]^T. Issued right after P[s] V[j-1]: the tensor pipe executes in order, so the
-      // overwrite of the aliased P columns cannot pass the read of P.
       auto issue_qk = [&](int s, int j) {
-        const int st = j & 1;
-        ptx::mbar_wait(&bar->k_full[st], (j >> 1) & 1);
+        const int st = j % kKV;
+        ptx::mbar_wait(&bar->k_full[st], (j / kKV) & 1);
         ptx::tc_fence_after();
-        issue_qk_steps(tmem_base + s * kBlockN, q_lo + s * kTile16, k_lo + st * kTile16, kIdescQK,
+        issue_qk_steps(tmem_base + s * 128 + (j & 1) * kBlockN, q_lo + s * kQTile16, k_lo + st * kTile16, kIdescQK,
                        std::make_integer_sequence<int, DH / 16>{});
-        ptx::tc_commit(&bar->s_full[s]);
+        ptx::tc_commit(&bar->s_full[s][j & 1]);
         if (s == 1 || j >= n_t1) ptx::tc_commit(&bar->k_empty[st]);  // last stage to read K[j]
       };
 #pragma unroll
-      for (int s = 0; s < kStages; ++s) {
-        if ((s ? n_t1 : n_t0) > 0) {
-          ptx::mbar_wait(&bar->q_full[s], 0);
-          issue_qk(s, 0);
-        }
+      for (int s = 0; s < kStages; ++s)
+        if ((s ? n_t1 : n_t0) > 0) ptx::mbar_wait(&bar->q_full[s], 0);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+#pragma unroll
+        for (int s = 0; s < kStages; ++s)
+          if (j < (s ? n_t1 : n_t0)) issue_qk(s, j);
       }
       for (int j = 0; j < n_max; ++j) {
-        const int st = j & 1;
-        const uint32_t ph = (j >> 1) & 1;
+        const int st = j % kKV;
 #pragma unroll
         for (int s = 0; s < kStages; ++s) {
-          if (j >= (s ? n_t1 : n_t0)) continue;
-          ptx::mbar_wait(&bar->v_full[st], ph);
-          ptx::mbar_wait(&bar->p_full[s], j & 1);
+          const int nt = s ? n_t1 : n_t0;
+          if (j >= nt) continue;
+          ptx::mbar_wait(&bar->v_full[st], (j / kKV) & 1);
+          ptx::mbar_wait(&bar->p_full[s][j & 1], (j >> 1) & 1);
           ptx::tc_fence_after();
-          issue_pv_steps(tmem_base + 2 * kBlockN + s * kBlockN, tmem_base + s * kBlockN, v_lo + st * kTile16, kIdescPV,
-                         j > 0, std::make_integer_sequence<int, kBlockN / 16>{});
+          issue_pv_steps(tmem_base + 256 + s * 128, tmem_base + s * 128 + (j & 1) * kBlockN, v_lo + st * kTile16,
+                         kIdescPV, j > 0, std::make_integer_sequence<int, kBlockN / 16>{});
           ptx::tc_commit(&bar->o_done[s]);
+          if (j == nt - 1) ptx::tc_commit(&bar->o_final[s]);
           if (s == 1 || j >= n_t1) ptx::tc_commit(&bar->v_empty[st]);  // last stage to read V[j]
-          if (j + 1 < (s ? n_t1 : n_t0)) issue_qk(s, j + 1);
+          if (j + 2 < nt) issue_qk(s, j + 2);
         }
       }
     }
@@ -411,36 +433,37 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     const int mt = pair * kStages + s;
     const int qrow = mt * kBlockM + row;          // row inside the sequence
     const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
-    const uint32_t s_addr = tmem_base + lane_off + s * kBlockN;
-    const uint32_t o_addr = tmem_base + lane_off + 2 * kBlockN + s * kBlockN;
+    const uint32_t s_base = tmem_base + lane_off + s * 128;
+    const uint32_t o_addr = tmem_base + lane_off + 256 + s * 128;
     const float scale2 = p.scale * kLog2e;
     const uint32_t bias_addr = ptx::smem_u32(s_bias);
     const int nt = s ? n_t1 : n_t0;
     float m_ref = -INFINITY, l = 0.f;
 
     for (int j = 0; j < nt; ++j) {
-      const int st = j & 1;
-      ptx::mbar_wait(&bar->bias_full[st], (j >> 1) & 1);
-      ptx::mbar_wait(&bar->s_full[s], j & 1);
+      const int bs = j % kBiasRing;
+      ptx::mbar_wait(&bar->bias_full[bs], (j / kBiasRing) & 1);
+      ptx::mbar_wait(&bar->s_full[s][j & 1], (j >> 1) & 1);
       ptx::tc_fence_after();
       const bool diag_tile = p.causal && (j * kBlockN + kBlockN - 1 > mt * kBlockM + diag);
       const int climit = qrow + diag - j * kBlockN;  // columns <= climit are visible
+      const uint32_t s_addr = s_base + (j & 1) * kBlockN;
       if (diag_tile)
-        softmax_tile<T, DH, true>(s_addr, o_addr, bias_addr + st * kBlockN * 4, scale2, climit, j == 0, &bar->o_done[s],
+        softmax_tile<T, DH, true>(s_addr, o_addr, bias_addr + bs * kBlockN * 4, scale2, climit, j == 0, &bar->o_done[s],
                                   (j - 1) & 1, m_ref, l);
       else
-        softmax_tile<T, DH, false>(s_addr, o_addr, bias_addr + st * kBlockN * 4, scale2, climit, j == 0, &bar->o_done[s],
-                                   (j - 1) & 1, m_ref, l);
+        softmax_tile<T, DH, false>(s_addr, o_addr, bias_addr + bs * kBlockN * 4, scale2, climit, j == 0,
+                                   &bar->o_done[s], (j - 1) & 1, m_ref, l);
       ptx::tc_wait_st();
       ptx::tc_fence_before();
-      ptx::mbar_arrive(&bar->p_full[s]);
+      ptx::mbar_arrive(&bar->p_full[s][j & 1]);
     }
 
     // ---- epilogue: O / l -> global ---------------------------------------------------------------
     const bool row_ok = qrow < len_q;
     T* out = reinterpret_cast<T*>(p.out) + (int64_t)(q0 + qrow) * p.out_row_stride + (int64_t)head * DH;
     if (nt > 0) {
-      ptx::mbar_wait(&bar->o_done[s], (nt - 1) & 1);
+      ptx::mbar_wait(&bar->o_final[s], 0);  // committed after the last P V of this stage
       ptx::tc_fence_after();
       const float inv = l > 0.f ? 1.0f / l : 0.f;
 #pragma unroll
@@ -492,8 +515,9 @@ EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-// rows x cols view of packed token rows; box = 128 rows x 64 elements, 128-byte swizzle.
-int make_tmap(CUtensorMap* m, const void* base, int dtype, int64_t cols, int64_t rows, int64_t row_stride_elems) {
+// rows x cols view of packed token rows; box = box_rows rows x 64 elements, 128-byte swizzle.
+int make_tmap(CUtensorMap* m, const void* base, int dtype, int64_t cols, int64_t rows, int64_t row_stride_elems,
+              int box_rows) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled not available from the driver");
@@ -501,7 +525,7 @@ int make_tmap(CUtensorMap* m, const void* base, int dtype, int64_t cols, int64_t
   }
   cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t gstride[1] = {(cuuint64_t)row_stride_elems * 2};
-  cuuint32_t box[2] = {64, (cuuint32_t)kBlockN};
+  cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(m, dtype == CRAM_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
                   const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -518,9 +542,9 @@ template <typename T, int DH>
 int launch_t(const cram_attn_prefill_params& p, cudaStream_t stream) {
   CUtensorMap tq, tk, tv;
   int rc;
-  if ((rc = make_tmap(&tq, p.q, p.dtype, (int64_t)p.n_heads * DH, p.total_q, p.q_row_stride)) != CRAM_OK) return rc;
-  if ((rc = make_tmap(&tk, p.k, p.dtype, (int64_t)p.n_kv_heads * DH, p.total_k, p.k_row_stride)) != CRAM_OK) return rc;
-  if ((rc = make_tmap(&tv, p.v, p.dtype, (int64_t)p.n_kv_heads * DH, p.total_k, p.v_row_stride)) != CRAM_OK) return rc;
+  if ((rc = make_tmap(&tq, p.q, p.dtype, (int64_t)p.n_heads * DH, p.total_q, p.q_row_stride, kBlockM)) != CRAM_OK) return rc;
+  if ((rc = make_tmap(&tk, p.k, p.dtype, (int64_t)p.n_kv_heads * DH, p.total_k, p.k_row_stride, kBlockN)) != CRAM_OK) return rc;
+  if ((rc = make_tmap(&tv, p.v, p.dtype, (int64_t)p.n_kv_heads * DH, p.total_k, p.v_row_stride, kBlockN)) != CRAM_OK) return rc;
   const int num_pairs = (p.max_seqlen_q + kStages * kBlockM - 1) / (kStages * kBlockM);
   const long long grid = (long long)num_pairs * p.n_seq * p.n_heads;
   if (grid == 0) return CRAM_OK;
