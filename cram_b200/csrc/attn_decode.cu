@@ -216,6 +216,23 @@ static int launch_decode_g(const cram_attn_decode_params& p, int n_splits, cudaS
   return rc;
 }
 
+static int launch_decode_combine(const cram_attn_decode_params& p, int n_splits, cudaStream_t stream) {
+  const float* part = reinterpret_cast<const float*>(p.workspace);
+  const dim3 grid(p.n_heads, p.n_seq);
+  if (p.dtype == CRAM_BF16) {
+    if (p.head_dim == 128)
+      attn_decode_combine_kernel<__nv_bfloat16, 128><<<grid, 128, 0, stream>>>(part, n_splits, p.n_heads, reinterpret_cast<__nv_bfloat16*>(p.out), p.out_row_stride);
+    else
+      attn_decode_combine_kernel<__nv_bfloat16, 64><<<grid, 64, 0, stream>>>(part, n_splits, p.n_heads, reinterpret_cast<__nv_bfloat16*>(p.out), p.out_row_stride);
+  } else {
+    if (p.head_dim == 128)
+      attn_decode_combine_kernel<__half, 128><<<grid, 128, 0, stream>>>(part, n_splits, p.n_heads, reinterpret_cast<__half*>(p.out), p.out_row_stride);
+    else
+      attn_decode_combine_kernel<__half, 64><<<grid, 64, 0, stream>>>(part, n_splits, p.n_heads, reinterpret_cast<__half*>(p.out), p.out_row_stride);
+  }
+  return check_launch("attn_decode_combine_kernel");
+}
+
 template <typename T, int DH>
 static int launch_decode_dh(const cram_attn_decode_params& p, int n_splits, cudaStream_t stream) {
   const int n_rep = p.n_heads / p.n_kv_heads;
@@ -233,6 +250,10 @@ static int launch_decode_t(const cram_attn_decode_params& p, int n_splits, cudaS
     default: set_error("cram_attn_decode: head_dim %d unsupported (64, 128)", p.head_dim); return CRAM_ERR_UNSUPPORTED;
   }
 }
+
+// tensor-core variant (attn_decode_mma.cu): bf16 / fp16, GQA group <= 16
+bool attn_decode_mma_supported(const cram_attn_decode_params& p);
+int launch_attn_decode_mma(const cram_attn_decode_params& p, int n_splits, cudaStream_t stream);
 
 }  // namespace cram
 
@@ -265,6 +286,11 @@ extern "C" int cram_attn_decode(const cram_attn_decode_params* pp, cram_stream_t
     }
   }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (attn_decode_mma_supported(p)) {
+    const int rc = launch_attn_decode_mma(p, n_splits, st);
+    if (rc != CRAM_OK || n_splits == 1) return rc;
+    return launch_decode_combine(p, n_splits, st);
+  }
   switch (p.dtype) {
     case CRAM_F32: return launch_decode_t<float>(p, n_splits, st);
     case CRAM_F16: return launch_decode_t<__half>(p, n_splits, st);

@@ -247,13 +247,43 @@ class CramEngine:
         return self.logits(x)
 
     @torch.no_grad()
+    def prefill_into_cache(self, prompts: Sequence[torch.Tensor], kv: PagedKV, block_table: torch.Tensor,
+                           logcreds: Optional[Sequence[torch.Tensor]] = None,
+                           head_masks: Optional[Sequence[int]] = None, chunk: int = 16) -> torch.Tensor:
+        """Re-weighted prefill of a batch of prompts (each a 1-D int64 CUDA tensor) into the paged cache,
+        `chunk` sequences per pass (bounds the activation footprint). Returns last-row logits [B, vocab]."""
+        dev, ps = self.device, kv.page_size
+        out = []
+        for b0 in range(0, len(prompts), chunk):
+            part = list(prompts[b0:b0 + chunk])
+            lens = [int(p.numel()) for p in part]
+            cu = torch.zeros(len(part) + 1, dtype=torch.int32)
+            cu[1:] = torch.tensor(lens, dtype=torch.int32).cumsum(0)
+            cu_d = cu.to(dev)
+            ids = torch.cat(part).to(dev)
+            positions = packed_positions(cu_d, ids.numel())
+            seq_of_row = torch.repeat_interleave(torch.arange(b0, b0 + len(part), device=dev), torch.tensor(lens, device=dev))
+            pos64 = positions.to(torch.int64)
+            slot = block_table[seq_of_row, pos64 // ps].to(torch.int64) * ps + pos64 % ps
+            lc = torch.cat(list(logcreds[b0:b0 + chunk])).to(dev) if logcreds is not None else None
+            x = self.prefill(ids, cu_d, max(lens), logcred=lc, head_masks=head_masks, kv=kv, slot_mapping=slot,
+                             positions=positions)
+            out.append(self.logits(x[(cu_d[1:] - 1).to(torch.int64)]))
+        return torch.cat(out)
+
+    @torch.no_grad()
     def generate(self, prompts: Sequence[torch.Tensor], logcreds: Optional[Sequence[torch.Tensor]] = None,
                  head_masks: Optional[Sequence[int]] = None, max_new_tokens: int = 100,
-                 eos_token_ids: Sequence[int] = (), bad_token_ids: Sequence[int] = (), page_size: int = 16) -> List[List[int]]:
+                 eos_token_ids: Sequence[int] = (), bad_token_ids: Sequence[int] = (), page_size: int = 16,
+                 use_graph: bool = True, eos_check_every: int = 8) -> List[List[int]]:
         """Greedy generation for a batch of prompts (each a 1-D int64 CUDA tensor) with per-sample
         credibility. Mirrors model.generate(do_sample=False, max_new_tokens=...) of
         utils/re_weighting.py:126-132: stop at EOS (the EOS token is kept), single-token bad words are
-        never emitted. Returns the new tokens of every sequence."""
+        never emitted. Returns the new tokens of every sequence.
+
+        The decode step is captured once in a CUDA graph (DecodeSession) and replayed; generated tokens
+        stay on the device and are read back every `eos_check_every` steps to test for EOS (tokens a
+        sequence produces after its EOS are discarded here, as HF pads them away)."""
         s, dev = self.spec, self.device
         B = len(prompts)
         lens = [int(p.numel()) for p in prompts]
@@ -261,49 +291,116 @@ class CramEngine:
         pages_per_seq = (max_total + page_size - 1) // page_size
         kv = PagedKV(s, B * pages_per_seq, page_size, self.dtype, dev)
         block_table = torch.arange(B * pages_per_seq, dtype=torch.int32, device=dev).view(B, pages_per_seq)
-        cu = torch.zeros(B + 1, dtype=torch.int32)
-        cu[1:] = torch.tensor(lens, dtype=torch.int32).cumsum(0)
-        cu_d = cu.to(dev)
-        ids = torch.cat(list(prompts)).to(dev)
-        positions = packed_positions(cu_d, ids.numel())
-        seq_of_row = torch.repeat_interleave(torch.arange(B, device=dev), torch.tensor(lens, device=dev))
-        pos64 = positions.to(torch.int64)
-        slot = block_table[seq_of_row, pos64 // page_size].to(torch.int64) * page_size + pos64 % page_size
-        lc_packed = torch.cat(list(logcreds)).to(dev) if logcreds is not None else None
-        x = self.prefill(ids, cu_d, max(lens), logcred=lc_packed, head_masks=head_masks, kv=kv, slot_mapping=slot,
-                         positions=positions)
-        last_rows = (cu_d[1:] - 1).to(torch.int64)
-        logits = self.logits(x[last_rows])
+        logits = self.prefill_into_cache(prompts, kv, block_table, logcreds, head_masks)
         # decode-time bias: [B, T0max] padded with zeros, keys < bias_len[b] biased
         lc_dec = bias_len = None
         if logcreds is not None:
-            lc_dec = torch.zeros(B, max(lens), dtype=lc_packed.dtype, device=dev)
+            lc_dec = torch.zeros(B, max(lens), dtype=logcreds[0].dtype, device=dev)
             for b, lc in enumerate(logcreds):
                 lc_dec[b, :lens[b]] = lc
             bias_len = torch.tensor(lens, dtype=torch.int32, device=dev)
         ban = torch.tensor(list(bad_token_ids), dtype=torch.int64, device=dev) if bad_token_ids else None
-        eos = torch.tensor(list(eos_token_ids), dtype=torch.int64, device=dev) if eos_token_ids else None
-        out = [[] for _ in range(B)]
+        if ban is not None:
+            logits[:, ban] = float("-inf")
+        first = logits.argmax(-1)
+        sess = DecodeSession(self, kv, block_table, lens, max_new_tokens, logcred=lc_dec, bias_len=bias_len,
+                             head_masks=head_masks, bad_token_ids=bad_token_ids, use_graph=use_graph)
+        sess.start(first)
+        eos = set(int(e) for e in eos_token_ids)
+        out: List[List[int]] = [[] for _ in range(B)]
         alive = [True] * B
-        cur_len = torch.tensor(lens, dtype=torch.int32, device=dev)
-        ws = None
-        for step in range(max_new_tokens):
-            if ban is not None:
-                logits[:, ban] = float("-inf")
-            nxt = logits.argmax(-1)
-            nxt_h = nxt.tolist()
-            for b in range(B):
-                if alive[b]:
-                    out[b].append(nxt_h[b])
-                    if eos is not None and nxt_h[b] in eos_token_ids:
-                        alive[b] = False
-            if not any(alive) or step == max_new_tokens - 1:
+        done_rows = 0
+
+        def drain(upto: int) -> None:
+            nonlocal done_rows
+            rows = sess.out_tokens[done_rows:upto].tolist()
+            for row in rows:
+                for b in range(B):
+                    if alive[b]:
+                        out[b].append(row[b])
+                        if row[b] in eos:
+                            alive[b] = False
+            done_rows = upto
+
+        produced = 1  # out_tokens[0] = the token chosen from the prefill logits
+        while True:
+            if produced % eos_check_every == 0 or produced == max_new_tokens or not eos:
+                if eos or produced == max_new_tokens:
+                    drain(produced)
+            if produced == max_new_tokens or not any(alive):
                 break
-            positions_d = cur_len.clone()
-            cur_len = cur_len + 1
-            logits = self.decode_step(nxt, positions_d, kv, block_table, cur_len, int(max(lens) + step + 1),
-                                      logcred=lc_dec, bias_len=bias_len, head_masks=head_masks, workspace=ws)
+            sess.step()
+            produced += 1
+        drain(produced)
         return out
+
+
+class DecodeSession:
+    """Greedy decode of a fixed batch over a paged KV cache with the whole per-token step -- embedding,
+    every layer (library GEMMs + libcram_b200 glue + the credibility-biased decode attention), final
+    norm, lm_head, bad-word ban, argmax and the position/length bookkeeping -- captured in ONE CUDA
+    graph and replayed per token: ~12 launches per layer collapse into one graph launch."""
+
+    def __init__(self, engine: CramEngine, kv: PagedKV, block_table: torch.Tensor, prompt_lens: Sequence[int],
+                 max_new_tokens: int, logcred: Optional[torch.Tensor] = None, bias_len: Optional[torch.Tensor] = None,
+                 head_masks: Optional[Sequence[int]] = None, bad_token_ids: Sequence[int] = (), use_graph: bool = True):
+        dev = engine.device
+        self.engine, self.kv, self.block_table = engine, kv, block_table
+        self.logcred, self.bias_len, self.head_masks = logcred, bias_len, head_masks
+        self.B = len(prompt_lens)
+        self.max_total = int(max(prompt_lens)) + int(max_new_tokens)
+        engine._ensure_rope(self.max_total + 1)
+        self.prompt_lens = torch.tensor(list(prompt_lens), dtype=torch.int32, device=dev)
+        self.tokens = torch.zeros(self.B, dtype=torch.int64, device=dev)
+        self.positions = torch.zeros(self.B, dtype=torch.int32, device=dev)   # index of the token being fed
+        self.seqlens = torch.zeros(self.B, dtype=torch.int32, device=dev)     # keys visible to it
+        self.out_tokens = torch.zeros(max_new_tokens, self.B, dtype=torch.int64, device=dev)
+        self.step_idx = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.ban = torch.tensor(list(bad_token_ids), dtype=torch.int64, device=dev) if bad_token_ids else None
+        self.use_graph = use_graph
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+
+    def _body(self) -> None:
+        logits = self.engine.decode_step(self.tokens, self.positions, self.kv, self.block_table, self.seqlens,
+                                         self.max_total, logcred=self.logcred, bias_len=self.bias_len,
+                                         head_masks=self.head_masks)
+        if self.ban is not None:
+            logits[:, self.ban] = float("-inf")
+        nxt = logits.argmax(-1)
+        self.out_tokens.index_copy_(0, self.step_idx, nxt[None])
+        self.tokens.copy_(nxt)
+        self.positions.add_(1)
+        self.seqlens.add_(1)
+        self.step_idx.add_(1)
+
+    def start(self, first_tokens: torch.Tensor) -> None:
+        """first_tokens: the token chosen from the prefill logits (new token 0 of every sequence)."""
+        self.tokens.copy_(first_tokens)
+        self.positions.copy_(self.prompt_lens)
+        self.seqlens.copy_(self.prompt_lens + 1)
+        self.out_tokens[0].copy_(first_tokens)
+        self.step_idx.fill_(1)
+        if self.use_graph and self.graph is None:
+            state = [t.clone() for t in (self.tokens, self.positions, self.seqlens, self.out_tokens, self.step_idx)]
+            side = torch.cuda.Stream(device=self.engine.device)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                self._body()  # warm-up: cuBLAS workspaces, kernel attributes (writes only cache slots >= prompt length)
+            torch.cuda.current_stream().wait_stream(side)
+            for t, c in zip((self.tokens, self.positions, self.seqlens, self.out_tokens, self.step_idx), state):
+                t.copy_(c)
+            torch.cuda.synchronize()
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                self._body()
+            for t, c in zip((self.tokens, self.positions, self.seqlens, self.out_tokens, self.step_idx), state):
+                t.copy_(c)  # capture does not execute, but keep the state explicit
+
+    def step(self) -> None:
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._body()
 
 
 def packed_positions(cu_seqlens: torch.Tensor, n_rows: int) -> torch.Tensor:

@@ -1,0 +1,6 @@
+# multi-GPU bench trip: bash scripts/trip_n.sh N  (run under gpurun --gpus N)
+N=${1:-2}
+mkdir -p gpurun_out
+timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
+  bench.py --gpus $N --steps 4 --warmup 3 > gpurun_out/bench_n$N.log 2> gpurun_out/bench_n$N.err; echo "bench n=$N rc=$?"
+tail -n 3 gpurun_out/bench_n$N.log; tail -n 5 gpurun_out/bench_n$N.err
