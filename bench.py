@@ -42,15 +42,23 @@ def parse():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=16)
-    ap.add_argument("--seq", type=int, default=2048)
-    ap.add_argument("--docs", type=int, default=5)
+    ap.add_argument("--workload", default="prefill", choices=["prefill", "decode", "longctx"],
+                    help="prefill = BASELINE configs[1] (the default bench line); decode = configs[3] (Qwen2-7B shapes, paged "
+                         "KV, batch 64, 256 new tokens); longctx = configs[4] (Llama-3-70B shapes, 20 docs / 32k tokens)")
+    ap.add_argument("--batch", type=int, default=0, help="0 = the workload's own (16 prefill, 64 decode, 1 longctx)")
+    ap.add_argument("--seq", type=int, default=0, help="0 = the workload's own (2048, 2048, 32768)")
+    ap.add_argument("--docs", type=int, default=0, help="0 = the workload's own (5, 5, 20)")
+    ap.add_argument("--new-tokens", type=int, default=256, help="decode workload: tokens generated per sequence per step")
+    ap.add_argument("--page-size", type=int, default=16)
     ap.add_argument("--layers", type=int, default=0, help="debug only: fewer layers (marks the line invalid)")
     ap.add_argument("--sweep-prompts", type=int, default=1, help="prompts for the IE-sweep sub-measurement (0 = skip)")
     ap.add_argument("--sweep-layers", type=int, default=0, help="debug only: sweep only the last k layers")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--attn-kernel", type=int, default=0, help="0 auto (tcgen05), 1 generic, 2 tcgen05")
-    return ap.parse_args()
+    a = ap.parse_args()
+    dflt = {"prefill": (16, 2048, 5), "decode": (64, 2048, 5), "longctx": (1, 32768, 20)}[a.workload]
+    a.batch, a.seq, a.docs = a.batch or dflt[0], a.seq or dflt[1], a.docs or dflt[2]
+    return a
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -194,40 +202,70 @@ def run_reference(args):
 # ---------------------------------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------------------------------
-def run_ours(args):
-    import torch.distributed as dist
+class Dist:
+    """One process per GPU (torchrun env); barrier + max/sum over ranks for the timing contract."""
 
+    def __init__(self):
+        import torch.distributed as dist
+        self.dist = dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py --impl ours needs a CUDA device: cram_b200 has no CPU fallback")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+
+    def _reduce(self, v: float, op) -> float:
+        if self.world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    def allmax(self, v: float) -> float:
+        return self._reduce(v, self.dist.ReduceOp.MAX)
+
+    def allsum(self, v: float) -> float:
+        return self._reduce(v, self.dist.ReduceOp.SUM)
+
+    def close(self):
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
+def timed_steps(D: Dist, fn, steps: int, sampler=None) -> float:
+    """EXACTLY `steps` calls of fn between barrier + synchronize, CUDA events, max over ranks -> ms per step."""
+    D.barrier(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if sampler is not None:
+        sampler.__enter__()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if sampler is not None:
+        sampler.__exit__()
+    D.barrier()
+    return D.allmax(e0.elapsed_time(e1) / steps)
+
+
+def run_ours(args):
     from cram_b200 import ops, synth
     from cram_b200.engine import LLAMA3_8B, CramEngine, ModelSpec
     from cram_b200.re_weighting import Find_Best_Heads, Re_Weighting_Strategy, _heads_dict_to_masks
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py --impl ours needs a CUDA device: cram_b200 has no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-
-    def allmax(v: float) -> float:
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def allsum(v: float) -> float:
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    D = Dist()
+    dist = D.dist
+    world, rank, local, dev = D.world, D.rank, D.local, D.dev
+    barrier, allmax, allsum = D.barrier, D.allmax, D.allsum
 
     spec = LLAMA3_8B
     if args.layers:
@@ -401,5 +439,11 @@ if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.workload == "decode":
+        from bench_workloads import run_decode
+        run_decode(a)
+    elif a.workload == "longctx":
+        from bench_workloads import run_longctx
+        run_longctx(a)
     else:
         run_ours(a)

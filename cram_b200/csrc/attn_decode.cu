@@ -254,6 +254,7 @@ static int launch_decode_t(const cram_attn_decode_params& p, int n_splits, cudaS
 // tensor-core variant (attn_decode_mma.cu): bf16 / fp16, GQA group <= 16
 bool attn_decode_mma_supported(const cram_attn_decode_params& p);
 int launch_attn_decode_mma(const cram_attn_decode_params& p, int n_splits, cudaStream_t stream);
+int attn_decode_mma_splits(const cram_attn_decode_params& p);
 
 }  // namespace cram
 
@@ -277,7 +278,9 @@ extern "C" int cram_attn_decode(const cram_attn_decode_params* pp, cram_stream_t
   CRAM_REQUIRE((p.page_stride * esz) % 16 == 0 && (p.token_stride * esz) % 16 == 0 && (p.head_dim * esz) % 16 == 0,
                "cram_attn_decode: cache strides must be 16-byte multiples");
   CRAM_REQUIRE(((uintptr_t)p.k_cache & 15) == 0 && ((uintptr_t)p.v_cache & 15) == 0, "cram_attn_decode: cache must be 16-byte aligned");
-  int n_splits = p.n_splits > 0 ? p.n_splits : choose_splits(p.n_seq, p.n_kv_heads, p.max_seqlen);
+  const bool use_mma = attn_decode_mma_supported(p);
+  int n_splits = p.n_splits > 0 ? p.n_splits
+                                : (use_mma ? attn_decode_mma_splits(p) : choose_splits(p.n_seq, p.n_kv_heads, p.max_seqlen));
   if (n_splits > 1) {
     const size_t need = (size_t)p.n_seq * p.n_heads * n_splits * (p.head_dim + 2) * sizeof(float);
     if (p.workspace == nullptr || p.workspace_bytes < need) {
@@ -286,7 +289,7 @@ extern "C" int cram_attn_decode(const cram_attn_decode_params* pp, cram_stream_t
     }
   }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (attn_decode_mma_supported(p)) {
+  if (use_mma) {
     const int rc = launch_attn_decode_mma(p, n_splits, st);
     if (rc != CRAM_OK || n_splits == 1) return rc;
     return launch_decode_combine(p, n_splits, st);

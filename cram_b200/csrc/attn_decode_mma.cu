@@ -3,7 +3,7 @@
 //
 // CTA = (split, kv head, sequence), 4 warps. The GQA group's query heads (<= 16) are the M rows of
 // mma.sync.m16n8k16 tiles, so the whole group is evaluated against each staged K/V tile and the
-// cache is streamed once per group. K/V tiles of 64 keys arrive through a 4-deep cp.async ring
+// cache is streamed once per group. K/V tiles of 64 keys arrive through a 3-deep cp.async ring
 // (16-byte chunks, XOR-swizzled rows so ldmatrix is conflict-free); warp w owns keys 16w..16w+15 of
 // every tile and keeps its own online-softmax state, the four states are merged once at the end.
 // The credibility bias is indexed by absolute key position and only applies to keys < bias_len
@@ -20,7 +20,8 @@ namespace {
 constexpr int kMmaThreads = 128;
 constexpr int kMmaWarps = 4;
 constexpr int kTileKeys = 64;
-constexpr int kRing = 4;
+constexpr int kRing = 3;        // 3 x 32 KB per CTA, two CTAs per SM: 128 KB of cache reads in flight per SM
+constexpr int kMaxSplitPages = 1024;  // page ids of one split staged in shared memory
 
 __device__ __forceinline__ void cp_async16_zfill(uint32_t smem, const void* gmem, bool valid) {
   const int n = valid ? 16 : 0;
@@ -76,8 +77,8 @@ __device__ __forceinline__ float fast_ex2(float x) {
 }
 
 // partial results: [n_seq, n_heads, n_splits, DH + 2] floats (o[DH] unnormalised, m, l)
-template <typename T, int DH>
-__global__ void __launch_bounds__(kMmaThreads)
+template <typename T, int DH, bool kPagePow2>
+__global__ void __launch_bounds__(kMmaThreads, 2)
 attn_decode_mma_kernel(const cram_attn_decode_params p, const int n_splits, float* __restrict__ part) {
   constexpr int CHUNKS = DH / 8;                 // 16-byte chunks per K/V row
   constexpr int ROW_BYTES = DH * 2;
@@ -119,11 +120,52 @@ attn_decode_mma_kernel(const cram_attn_decode_params p, const int n_splits, floa
     }
   }
 
-  const int32_t* bt = p.block_table + (int64_t)seq * p.block_table_stride;
+  // page ids of this split -> shared memory (the block-table load would otherwise sit on the critical
+  // path of every cp.async address)
+  int32_t* s_pages = reinterpret_cast<int32_t*>(dsm + kRing * STAGE_BYTES);
+  const int page0 = k_begin / p.page_size;
+  {
+    const int32_t* bt = p.block_table + (int64_t)seq * p.block_table_stride;
+    const int n_pages = k_end > k_begin ? (k_end - 1) / p.page_size - page0 + 1 : 0;
+    for (int i = threadIdx.x; i < n_pages; i += kMmaThreads) s_pages[i] = bt[page0 + i];
+  }
+  if (any_bias) {
+    // pull this split's slice of the bias row towards L2 now: under a saturated HBM a first-touch miss
+    // costs more than one tile iteration, which is all the register prefetch below can hide
+    const int esz = p.logcred_dtype == CRAM_F32 ? 4 : 2;
+    const uint8_t* b0 = reinterpret_cast<const uint8_t*>(p.logcred) + ((int64_t)seq * p.logcred_stride + k_begin) * esz;
+    const int nbytes = (min(k_end, bias_len) - k_begin) * esz;
+    for (int off = threadIdx.x * 128; off < nbytes; off += kMmaThreads * 128)
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(b0 + off));
+  }
+  __syncthreads();
   const uint8_t* kc = reinterpret_cast<const uint8_t*>(p.k_cache);
   const uint8_t* vc = reinterpret_cast<const uint8_t*>(p.v_cache);
   const int ld_chunk = threadIdx.x % CHUNKS, ld_row0 = threadIdx.x / CHUNKS;
 
+  const int page_shift = kPagePow2 ? 31 - __clz(p.page_size) : 0;
+  // this thread's 4 bias values of tile t, fetched one tile ahead of their use as RAW bits (the
+  // conversion and the x log2e happen at the use, so the loads stay in flight across the iteration)
+  auto load_bias = [&](int t, uint32_t (&b)[4]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int pos = k_begin + t * kTileKeys + warp * 16 + (i >> 1) * 8 + qd * 2 + (i & 1);
+      uint32_t raw = 0u;  // +0.0 in every dtype
+      if (any_bias && pos < bias_len && pos < k_end) {
+        const int64_t idx = (int64_t)seq * p.logcred_stride + pos;
+        raw = p.logcred_dtype == CRAM_F32 ? reinterpret_cast<const uint32_t*>(p.logcred)[idx]
+                                          : (uint32_t) reinterpret_cast<const uint16_t*>(p.logcred)[idx];
+      }
+      b[i] = raw;
+    }
+  };
+  auto bias_value = [&](uint32_t raw) -> float {
+    float f;
+    if (p.logcred_dtype == CRAM_BF16) f = __uint_as_float(raw << 16);
+    else if (p.logcred_dtype == CRAM_F16) f = __half2float(__ushort_as_half((unsigned short)raw));
+    else f = __uint_as_float(raw);
+    return f * kLog2e;
+  };
   auto load_tile = [&](int t) {
     const uint32_t st = smem0 + (t % kRing) * STAGE_BYTES;
     const int kb = k_begin + t * kTileKeys;
@@ -132,8 +174,9 @@ attn_decode_mma_kernel(const cram_attn_decode_params p, const int n_splits, floa
       const int pos = kb + r;
       const bool ok = pos < k_end;
       const int ps = ok ? pos : k_begin;
-      const int64_t page = bt[ps / p.page_size];
-      const int64_t off = (page * p.page_stride + (int64_t)(ps % p.page_size) * p.token_stride + (int64_t)kvh * DH) * 2 +
+      const int pg = kPagePow2 ? (ps >> page_shift) : ps / p.page_size;
+      const int64_t page = s_pages[pg - page0];
+      const int64_t off = (page * p.page_stride + (int64_t)(ps - pg * p.page_size) * p.token_stride + (int64_t)kvh * DH) * 2 +
                           ld_chunk * 16;
       const uint32_t dst = st + r * ROW_BYTES + ((ld_chunk ^ (r & 7)) << 4);
       cp_async16_zfill(dst, kc + off, ok);
@@ -151,12 +194,22 @@ attn_decode_mma_kernel(const cram_attn_decode_params p, const int n_splits, floa
     if (t < n_tiles) load_tile(t);
     cp_async_commit();
   }
+  uint32_t bnext[4], bnext2[4];
+  load_bias(0, bnext);
+  load_bias(1, bnext2);
 
   for (int t = 0; t < n_tiles; ++t) {
     cp_async_wait<kRing - 2>();
     __syncthreads();  // tile t has landed for every thread; everyone is done with tile t-1's slot
     if (t + kRing - 1 < n_tiles) load_tile(t + kRing - 1);
     cp_async_commit();
+    uint32_t bcur[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      bcur[i] = bnext[i];
+      bnext[i] = bnext2[i];
+    }
+    load_bias(t + 2, bnext2);
 
     const uint32_t sK = smem0 + (t % kRing) * STAGE_BYTES, sV = sK + TILE_BYTES;
     const int key0 = warp * 16;                       // this warp's keys inside the tile
@@ -186,9 +239,7 @@ attn_decode_mma_kernel(const cram_attn_decode_params p, const int n_splits, floa
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int pos = pos0 + nt * 8 + qd * 2 + e;
-        float bias = 0.f;
-        if (any_bias && pos < bias_len && pos < k_end)
-          bias = load_logcred(p.logcred, (int64_t)seq * p.logcred_stride + pos, p.logcred_dtype) * kLog2e;
+        const float bias = bias_value(bcur[nt * 2 + e]);
         const bool vis = pos < k_end;
         t0[nt * 2 + e] = vis ? fmaf(s[nt][e], scale2, hb0 ? bias : 0.f) : -INFINITY;
         t1[nt * 2 + e] = vis ? fmaf(s[nt][2 + e], scale2, hb1 ? bias : 0.f) : -INFINITY;
@@ -297,14 +348,15 @@ attn_decode_mma_kernel(const cram_attn_decode_params p, const int n_splits, floa
 
 template <typename T, int DH>
 int launch_mma_t(const cram_attn_decode_params& p, int n_splits, cudaStream_t stream) {
-  constexpr size_t ring = (size_t)kRing * 2 * kTileKeys * DH * 2;
+  constexpr size_t ring = (size_t)kRing * 2 * kTileKeys * DH * 2 + kMaxSplitPages * sizeof(int32_t);
   constexpr size_t red = (size_t)kMmaWarps * 16 * (DH + 2) * sizeof(float);
   constexpr size_t smem = ring > red ? ring : red;
-  auto kern = attn_decode_mma_kernel<T, DH>;
-  static bool attr_set = false;  // per template instantiation
-  if (!attr_set) {
+  const bool pow2 = (p.page_size & (p.page_size - 1)) == 0;
+  auto kern = pow2 ? attn_decode_mma_kernel<T, DH, true> : attn_decode_mma_kernel<T, DH, false>;
+  static bool attr_set[2] = {false, false};  // per template instantiation
+  if (!attr_set[pow2]) {
     CRAM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
+    attr_set[pow2] = true;
   }
   dim3 grid(n_splits, p.n_kv_heads, p.n_seq);
   kern<<<grid, kMmaThreads, smem, stream>>>(p, n_splits, reinterpret_cast<float*>(p.workspace));
@@ -318,7 +370,29 @@ bool attn_decode_mma_supported(const cram_attn_decode_params& p) {
          p.n_heads / p.n_kv_heads <= 16 && p.q_row_stride % 2 == 0 && (reinterpret_cast<uintptr_t>(p.q) & 3) == 0;
 }
 
+// splits: fill the resident CTA slots (2 per SM) once; never fewer than the page table staging allows
+int attn_decode_mma_splits(const cram_attn_decode_params& p) {
+  const int base = p.n_seq * p.n_kv_heads;
+  int want = (2 * sm_count()) / (base > 0 ? base : 1);
+  const int max_by_len = (p.max_seqlen + 4 * kTileKeys - 1) / (4 * kTileKeys);  // >= 256 keys per split
+  if (want > max_by_len) want = max_by_len;
+  if (want > 64) want = 64;
+  const int min_by_pages = (int)(((int64_t)p.max_seqlen + (int64_t)kMaxSplitPages * p.page_size - 1) /
+                                 ((int64_t)kMaxSplitPages * p.page_size));
+  if (want < min_by_pages) want = min_by_pages;
+  return want < 1 ? 1 : want;
+}
+
 int launch_attn_decode_mma(const cram_attn_decode_params& p, int n_splits, cudaStream_t stream) {
+  {
+    // one split may cover at most kMaxSplitPages pages (+1 tile of slack for the rounding of per_split)
+    const int64_t per_split = (((int64_t)p.max_seqlen + n_splits - 1) / n_splits + kTileKeys - 1) / kTileKeys * kTileKeys;
+    if (per_split / p.page_size + 2 > kMaxSplitPages) {
+      set_error("cram_attn_decode: %d splits leave %lld keys per split; at most %d pages of %d fit", n_splits,
+                (long long)per_split, kMaxSplitPages - 2, p.page_size);
+      return CRAM_ERR_INVALID;
+    }
+  }
   if (p.dtype == CRAM_BF16)
     return p.head_dim == 128 ? launch_mma_t<__nv_bfloat16, 128>(p, n_splits, stream)
                              : launch_mma_t<__nv_bfloat16, 64>(p, n_splits, stream);

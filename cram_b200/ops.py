@@ -20,6 +20,8 @@ _DT = {torch.float32: CRAM_F32, torch.float16: CRAM_F16, torch.bfloat16: CRAM_BF
 launch_count = 0
 # when a list, attn_prefill appends a (start, end) CUDA-event pair per launch, recorded on the launching stream
 attn_events = None
+# same for attn_decode (split-KV kernel + combine)
+decode_events = None
 
 
 def dtype_code(dt: torch.dtype) -> int:
@@ -174,7 +176,13 @@ def attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, b
         nbytes = lib.cram_attn_decode_workspace_bytes(n_seq, n_heads, head_dim, int(max_seqlen), n_splits)
         workspace = torch.empty(nbytes, dtype=torch.uint8, device=q.device)
     p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
+    if decode_events is not None:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
     check(lib.cram_attn_decode(C.byref(p), _stream()), "cram_attn_decode")
+    if decode_events is not None:
+        ev1.record()
+        decode_events.append((ev0, ev1))
     launch_count += 2
     return out
 

@@ -261,6 +261,47 @@ def llama_forward(sd: Dict[str, torch.Tensor], spec: ModelSpec, input_ids: torch
     return logits
 
 
+def decode_step_cached(sd: Dict[str, torch.Tensor], spec: ModelSpec, token_ids: torch.Tensor, position: int,
+                       k_cache: List[Optional[torch.Tensor]], v_cache: List[Optional[torch.Tensor]],
+                       hooks: Optional[Dict[int, Tuple[torch.Tensor, Sequence[int]]]] = None) -> torch.Tensor:
+    """One cached decode step [b,1] -> logits [b,V] the way model.generate runs it under the hook
+    (utils/re_weighting.py:126-132): q_len = 1, K/V appended to the per-layer cache (k_cache[l] is
+    [b,Hkv,k,dh] or None), and the hook's tgt_len == 1 branch (:39-48) turns the all-zero decode mask
+    into [b,H,1,k] with logcred on the first T0 key columns of the hooked heads (:56-59)."""
+    hooks = hooks or {}
+    dtype = sd["model.embed_tokens.weight"].dtype
+    b = token_ids.shape[0]
+    x = torch.nn.functional.embedding(token_ids.view(b, 1), sd["model.embed_tokens.weight"])
+    cos, sin = rope_cos_sin(spec, torch.full((b, 1), position), dtype)
+    cos, sin = cos[:, None], sin[:, None]
+    H, Hkv, dh = spec.num_heads, spec.num_kv_heads, spec.head_dim
+    lin = torch.nn.functional.linear
+    for l in range(spec.num_layers):
+        p = f"model.layers.{l}."
+        h = rmsnorm(x, sd[p + "input_layernorm.weight"], spec.rms_eps)
+        q = lin(h, sd[p + "self_attn.q_proj.weight"], sd.get(p + "self_attn.q_proj.bias")).view(b, 1, H, dh).transpose(1, 2)
+        k = lin(h, sd[p + "self_attn.k_proj.weight"], sd.get(p + "self_attn.k_proj.bias")).view(b, 1, Hkv, dh).transpose(1, 2)
+        v = lin(h, sd[p + "self_attn.v_proj.weight"], sd.get(p + "self_attn.v_proj.bias")).view(b, 1, Hkv, dh).transpose(1, 2)
+        q = q * cos + rotate_half(q) * sin
+        k = k * cos + rotate_half(k) * sin
+        k_cache[l] = k if k_cache[l] is None else torch.cat([k_cache[l], k], dim=2)
+        v_cache[l] = v if v_cache[l] is None else torch.cat([v_cache[l], v], dim=2)
+        src = k_cache[l].shape[2]
+        if l in hooks:
+            logcred, heads = hooks[l]
+            mask = edit_attention_mask(None, logcred[..., :src], heads, H, 1, src, dtype)
+        else:
+            mask = torch.zeros(1, 1, 1, src, dtype=dtype)
+        a = eager_attention(q, k_cache[l], v_cache[l], mask, dh ** -0.5).reshape(b, 1, H * dh)
+        x = x + lin(a, sd[p + "self_attn.o_proj.weight"])
+        h = rmsnorm(x, sd[p + "post_attention_layernorm.weight"], spec.rms_eps)
+        x = x + lin(torch.nn.functional.silu(lin(h, sd[p + "mlp.gate_proj.weight"])) * lin(h, sd[p + "mlp.up_proj.weight"]),
+                    sd[p + "mlp.down_proj.weight"])
+    x = rmsnorm(x, sd["model.norm.weight"], spec.rms_eps)
+    head = sd["model.embed_tokens.weight"] if spec.tie_embeddings else sd["lm_head.weight"]
+    return lin(x, head)[:, 0]
+
+
 def answer_logit_sum(logits: torch.Tensor, answer_ids: torch.Tensor) -> torch.Tensor:
     """utils/re_weighting.py:160: logits[0, -n:][arange(n), answer_ids].sum() in model dtype."""
     n = len(answer_ids)

@@ -20,15 +20,25 @@ seqlens = torch.tensor(lens, dtype=torch.int32, device=dev)
 lc = torch.zeros(B, 2048, device=dev).bfloat16(); lc[:, 100:900] = -0.69
 bl = torch.full((B,), 2048, dtype=torch.int32, device=dev)
 kv_bytes = sum(lens) * 2 * Hkv * dh * 2
+ws = torch.empty(ops._lib.load().cram_attn_decode_workspace_bytes(B, H, dh, max(lens), 0), dtype=torch.uint8, device=dev)
+out = torch.empty(B, H * dh, dtype=torch.bfloat16, device=dev)
+n_in_graph = 24
 for splits in splits_list:
     for mask, name in ((0, "clean"), (0x0FFFFFF, "biased24")):
-        for i in range(3):
-            ops.attn_decode(q, kc[i % n_layers], vc[i % n_layers], bt, seqlens, max(lens), H, Hkv, dh, logcred=lc, head_mask=mask, bias_len=bl, n_splits=splits)
+        def launches():
+            for i in range(n_in_graph):  # the Python call costs more than the kernel: time a CUDA graph of launches
+                ops.attn_decode(q, kc[i % n_layers], vc[i % n_layers], bt, seqlens, max(lens), H, Hkv, dh, logcred=lc,
+                                head_mask=mask, bias_len=bl, n_splits=splits, workspace=ws, out=out)
+        launches()
         torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            launches()
+        g.replay(); torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for i in range(reps):
-            ops.attn_decode(q, kc[i % n_layers], vc[i % n_layers], bt, seqlens, max(lens), H, Hkv, dh, logcred=lc, head_mask=mask, bias_len=bl, n_splits=splits)
+        for _ in range(reps):
+            g.replay()
         e1.record(); torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / reps
+        ms = e0.elapsed_time(e1) / (reps * n_in_graph)
         print(f"splits={splits} {name}: {ms*1e3:.1f} us/launch  {kv_bytes / ms / 1e6:.0f} GB/s of KV ({kv_bytes/1e6:.0f} MB)")

@@ -1,0 +1,5 @@
+mkdir -p gpurun_out
+run() { name=$1; shift; timeout $1 "${@:2}" > gpurun_out/$name.log 2>&1; echo "== $name rc=$?"; tail -n ${TAILN:-12} gpurun_out/$name.log; }
+TAILN=30 run t_decode 600 python -m pytest tests/test_decode_gpu.py -q -x
+TAILN=30 run t_engine 900 python -m pytest tests/test_engine_gpu.py -q -x
+TAILN=20 run prof_decode 300 python scripts/profile_decode.py 30 0,1,2,3,4,6,8

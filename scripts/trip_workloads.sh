@@ -1,0 +1,5 @@
+mkdir -p gpurun_out
+run() { name=$1; shift; timeout $1 "${@:2}" > gpurun_out/$name.log 2>&1; echo "== $name rc=$?"; tail -n ${TAILN:-12} gpurun_out/$name.log; }
+TAILN=30 run t_decode 600 python -m pytest tests/test_decode_gpu.py tests/test_engine_gpu.py -q -x
+TAILN=8 run prof_decode 300 python scripts/profile_decode.py 30 0,1,2,4
+TAILN=8 run bench_decode 1500 python bench.py --workload decode --steps 3 --warmup 3

@@ -127,3 +127,44 @@ def test_bf16_tracks_oracle_bf16_within_bf16_noise(gold):
         assert e_ours <= 2 * e_ref + 1e-2
         agree = (got.argmax(-1) == want16.argmax(-1)).float().mean().item()
         assert agree >= 0.97
+
+
+def test_graph_decode_equals_eager_and_oracle_cached_decode():
+    """Batch of ragged prompts, per-sample credibility, Qwen2-style QKV bias: the CUDA-graph decode session
+    produces the tokens of the eager loop, and (fp32) the tokens of the oracle's cached hooked decode."""
+    from oracle.tiny_model import random_state_dict
+    ospec = orc.ModelSpec(2, 8, 2, 64, 256, 384, 300, rms_eps=1e-6, rope_theta=10000.0, qkv_bias=True)
+    sd = random_state_dict(ospec, seed=11, dtype=torch.float32)
+    spec = ModelSpec(2, 8, 2, 64, 256, 384, 300, 1e-6, 10000.0, qkv_bias=True)
+    eng = CramEngine.from_state_dict(spec, sd, device=DEV)
+    g = torch.Generator().manual_seed(2)
+    lens = [37, 90, 64]
+    prompts = [torch.randint(3, 300, (n,), generator=g) for n in lens]
+    creds = []
+    for n in lens:
+        c = torch.ones(n, dtype=torch.float16)
+        c[4:n // 2] = 0.3
+        c[n // 2:n - 6] = 0.0
+        creds.append(c)
+    masks = [0b10110101, 0b00001111]
+    hooks_heads = {0: [0, 2, 4, 5, 7], 1: [0, 1, 2, 3]}
+    lcs = [ops.log_cred(c.to(DEV), torch.float32) for c in creds]
+    dev_prompts = [p.to(DEV) for p in prompts]
+    new = 12
+    got_graph = eng.generate(dev_prompts, lcs, masks, max_new_tokens=new, use_graph=True)
+    got_eager = eng.generate(dev_prompts, lcs, masks, max_new_tokens=new, use_graph=False)
+    assert got_graph == got_eager
+    for b, n in enumerate(lens):
+        lc = torch.log(creds[b]).float()[None]
+        hooks = {l: (lc, h) for l, h in hooks_heads.items()}
+        kc, vc = [None] * 2, [None] * 2
+        with torch.no_grad():
+            for t in range(n):
+                hk = {l: (lc[:, :t + 1], h) for l, (lc_, h) in hooks.items()}
+                logits = orc.decode_step_cached(sd, ospec, prompts[b][t:t + 1], t, kc, vc, hk)
+            want = []
+            for t in range(new):
+                nxt = int(logits[0].argmax())
+                want.append(nxt)
+                logits = orc.decode_step_cached(sd, ospec, torch.tensor([nxt]), n + t, kc, vc, hooks)
+        assert got_graph[b] == want, (b, got_graph[b], want)

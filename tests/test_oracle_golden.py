@@ -97,3 +97,28 @@ def test_tiny_model_logits_and_ie(golden_dir):
         assert abs(float(ori) - float(g["ie_ori_logit_sum"])) <= 2e-4
         cur = orc.answer_logit_sum(orc.llama_forward(sd, spec, ids2, {1: (lc2, [2])}), ans)
         assert abs(float(ori - cur) - g["ie_ref"][1, 2]) <= 2e-4
+
+
+def test_cached_decode_step_equals_full_recompute():
+    """The oracle's cached decode step (hook's tgt_len == 1 branch, re_weighting.py:39-48,56-59) gives
+    the logits of a full hooked forward over the same prefix (greedy_generate's docstring claim)."""
+    spec = orc.ModelSpec(2, 4, 2, 16, 32, 64, 50, rms_eps=1e-5, rope_theta=10000.0, qkv_bias=True)
+    from oracle.tiny_model import random_state_dict
+    sd = random_state_dict(spec, seed=3, dtype=torch.float32)
+    g = torch.Generator().manual_seed(1)
+    T0, T = 9, 13
+    ids = torch.randint(0, 50, (1, T), generator=g)
+    lc = torch.zeros(1, T0)
+    lc[:, 2:6] = float(np.log(np.float16(0.3)))
+    lc[:, 6:8] = float("-inf")
+    hooks = {0: (lc, [1, 3]), 1: (lc, [0])}
+    kc, vc = [None] * spec.num_layers, [None] * spec.num_layers
+    with torch.no_grad():
+        for t in range(T):
+            # during the prompt the bias only exists for keys < T0 that already are in the cache
+            step = orc.decode_step_cached(sd, spec, ids[:, t], t, kc, vc, hooks)
+            if t >= T0 - 1:
+                ext = torch.zeros(1, t + 1)
+                ext[:, :T0] = lc[:, :t + 1][:, :T0]
+                full = orc.llama_forward(sd, spec, ids[:, :t + 1], {l: (ext, h) for l, (_, h) in hooks.items()})[0, -1]
+                assert torch.allclose(step[0], full, atol=2e-5, rtol=1e-5), t
