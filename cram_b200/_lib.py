@@ -94,7 +94,7 @@ def load(build_if_missing: bool = True):
     with _lock:
         if _lib is not None:
             return _lib
-        path = _build.LIB_PATH
+        path = os.environ.get("CRAM_B200_LIB") or _build.LIB_PATH  # override: debug builds (scripts/trace_attn.py)
         if not os.path.exists(path):
             if not build_if_missing:
                 raise CramError(f"{path} is missing; run `python -m cram_b200.build` (no CPU fallback exists)")

@@ -44,6 +44,20 @@ constexpr int kTmemCols = 512;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
 
+// Debug timeline (scripts/trace_attn.py builds a separate library with -DCRAM_ATTN_TRACE=<block>; the product
+// build compiles none of this): clock64 stamps of one CTA's softmax warps, MMA issuer and producer, per tile.
+#ifdef CRAM_ATTN_TRACE
+__device__ long long g_trace[12][64][4];
+#define CRAM_TRACE(slot, j, e)                                                              \
+  do {                                                                                      \
+    if (blockIdx.x == CRAM_ATTN_TRACE && (j) < 64) g_trace[slot][j][e] = clock64();         \
+  } while (0)
+#else
+#define CRAM_TRACE(slot, j, e) \
+  do {                         \
+  } while (0)
+#endif
+
 struct Barriers {
   uint64_t q_full[2];
   uint64_t k_full[kKV], k_empty[kKV];
@@ -413,15 +427,19 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         for (int s = 0; s < kStages; ++s) {
           const int nt = s ? n_t1 : n_t0;
           if (j >= nt) continue;
+          CRAM_TRACE(8 + s, j, 0);
           ptx::mbar_wait(&bar->v_full[st], (j / kKV) & 1);
+          CRAM_TRACE(8 + s, j, 1);
           ptx::mbar_wait(&bar->p_full[s][j & 1], (j >> 1) & 1);
           ptx::tc_fence_after();
+          CRAM_TRACE(8 + s, j, 2);
           issue_pv_steps(tmem_base + 256 + s * 128, tmem_base + s * 128 + (j & 1) * kBlockN, v_lo + st * kTile16,
                          kIdescPV, j > 0, std::make_integer_sequence<int, kBlockN / 16>{});
           ptx::tc_commit(&bar->o_done[s]);
           if (j == nt - 1) ptx::tc_commit(&bar->o_final[s]);
           if (s == 1 || j >= n_t1) ptx::tc_commit(&bar->v_empty[st]);  // last stage to read V[j]
           if (j + 2 < nt) issue_qk(s, j + 2);
+          CRAM_TRACE(8 + s, j, 3);
         }
       }
     }
@@ -442,9 +460,11 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
 
     for (int j = 0; j < nt; ++j) {
       const int bs = j % kBiasRing;
+      if (lane == 0) CRAM_TRACE(warp, j, 0);
       ptx::mbar_wait(&bar->bias_full[bs], (j / kBiasRing) & 1);
       ptx::mbar_wait(&bar->s_full[s][j & 1], (j >> 1) & 1);
       ptx::tc_fence_after();
+      if (lane == 0) CRAM_TRACE(warp, j, 1);
       const bool diag_tile = p.causal && (j * kBlockN + kBlockN - 1 > mt * kBlockM + diag);
       const int climit = qrow + diag - j * kBlockN;  // columns <= climit are visible
       const uint32_t s_addr = s_base + (j & 1) * kBlockN;
@@ -454,9 +474,11 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       else
         softmax_tile<T, DH, false>(s_addr, o_addr, bias_addr + bs * kBlockN * 4, scale2, climit, j == 0,
                                    &bar->o_done[s], (j - 1) & 1, m_ref, l);
+      if (lane == 0) CRAM_TRACE(warp, j, 2);
       ptx::tc_wait_st();
       ptx::tc_fence_before();
       ptx::mbar_arrive(&bar->p_full[s][j & 1]);
+      if (lane == 0) CRAM_TRACE(warp, j, 3);
     }
 
     // ---- epilogue: O / l -> global ---------------------------------------------------------------
@@ -583,3 +605,9 @@ int launch_attn_sm100(const cram_attn_prefill_params& p, cudaStream_t stream) {
 }
 
 }  // namespace cram
+
+#ifdef CRAM_ATTN_TRACE
+extern "C" int cram_debug_read_trace(long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, cram::g_trace, sizeof(cram::g_trace)) == cudaSuccess ? 0 : -1;
+}
+#endif

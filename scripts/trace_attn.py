@@ -1,0 +1,60 @@
+"""Debug timeline of the tcgen05 attention kernel: builds a -DCRAM_ATTN_TRACE=<block> copy of the library
+(cram_b200/_build/libcram_b200_trace.so, not the product), runs one launch at the bench shape and prints, for the
+traced CTA, per-tile clock deltas of the softmax warps (stage 0 = warp 0, stage 1 = warp 4) and the MMA issuer.
+
+    python scripts/trace_attn.py build [block]      (CPU box: cross-compile)
+    python scripts/trace_attn.py run                (GPU box)
+"""
+import ctypes, os, subprocess, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+OUT = os.path.join(ROOT, "cram_b200", "_build", "libcram_b200_trace.so")
+
+def build(block, extra=(), out=OUT):
+    from cram_b200 import build as b
+    srcs = [os.path.join(b.CSRC, s) for s in b.SOURCES]
+    flags = [f for f in b.NVCC_FLAGS if f not in ("-Xptxas", "-v")]
+    defs = ([f"-DCRAM_ATTN_TRACE={block}"] if block >= 0 else []) + [f"-D{d}" for d in extra]
+    cmd = [b._nvcc(), *flags, *defs, "-shared", "-o", out, *srcs, "-cudart", "static"]
+    subprocess.run(cmd, check=True)
+    print("built", out)
+
+def run():
+    os.environ["CRAM_B200_LIB"] = OUT
+    import numpy as np, torch
+    from cram_b200 import ops, _lib
+    B, T, H, Hkv, dh = 16, 2048, 32, 8, 128
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(0)
+    lens = [T - 3 * i for i in range(B)]
+    total = sum(lens)
+    qkv = torch.randn(total, (H + 2 * Hkv) * dh, device=dev, generator=g).bfloat16()
+    q, k, v = qkv[:, :H * dh], qkv[:, H * dh:(H + Hkv) * dh], qkv[:, (H + Hkv) * dh:]
+    cu = torch.zeros(B + 1, dtype=torch.int32); cu[1:] = torch.tensor(lens).cumsum(0); cu = cu.to(dev)
+    lc = torch.zeros(total, device=dev).bfloat16(); lc[100:900] = -0.69
+    for _ in range(3):
+        ops.attn_prefill(q, k, v, cu, T, H, Hkv, dh, logcred=lc, head_mask=0x0FFFFFFF, kernel=2)
+    torch.cuda.synchronize()
+    lib = _lib.load()
+    buf = np.zeros((12, 64, 4), dtype=np.int64)
+    lib.cram_debug_read_trace.argtypes = [ctypes.c_void_p]
+    assert lib.cram_debug_read_trace(buf.ctypes.data) == 0
+    t0 = buf[buf > 0].min()
+    for slot, name in ((0, "softmax stage0 (warp 0)"), (4, "softmax stage1 (warp 4)"), (8, "mma stage0"), (9, "mma stage1")):
+        print(f"--- {name}: per tile [e0 rel start] d(e0->e1) d(e1->e2) d(e2->e3) | iteration period")
+        prev = None
+        for j in range(64):
+            e = buf[slot, j]
+            if e[0] == 0:
+                break
+            per = (e[0] - prev) if prev is not None else 0
+            prev = e[0]
+            print(f"  j={j:2d} start={e[0]-t0:7d}  {e[1]-e[0]:6d} {e[2]-e[1]:6d} {e[3]-e[2]:6d} | {per:6d}")
+
+if __name__ == "__main__":
+    if sys.argv[1] == "build":      # build <block | -1 = no trace> [DEFINE=VAL ...] [out=path]
+        outs = [a[4:] for a in sys.argv[3:] if a.startswith("out=")]
+        build(int(sys.argv[2]) if len(sys.argv) > 2 else 0, [a for a in sys.argv[3:] if not a.startswith("out=")],
+              outs[0] if outs else OUT)
+    else:
+        run()
