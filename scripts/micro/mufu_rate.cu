@@ -26,6 +26,9 @@ __global__ void k(uint32_t* out, long long* cyc, int iters) {
       if (MODE == 5) asm volatile("cvt.rn.bf16x2.f32 %0, %0, %1;" : "+r"(x[i]) : "r"(x[(i + 1) & 15]));
       if (MODE == 6) asm volatile("{.reg .b16 a, b; mov.b32 {a, b}, %0; ex2.approx.f16 a, a; mov.b32 %0, {a, b};}" : "+r"(x[i]));
       if (MODE == 7) asm volatile("fma.rn.f32 %0, %0, %0, %0;" : "+r"(x[i]));
+      if (MODE == 12) asm volatile("add.rn.f16x2 %0, %0, %1;" : "+r"(x[i]) : "r"(x[(i + 1) & 15]));
+      if (MODE == 13) asm volatile("cvt.rn.f16x2.f32 %0, %0, %1;" : "+r"(x[i]) : "r"(x[(i + 1) & 15]));
+      if (MODE == 14) asm volatile("{.reg .b16 a, b; mov.b32 {a, b}, %0; cvt.f32.f16 %0, a;}" : "+r"(x[i]));
     }
   }
   long long t1 = clock64();
@@ -50,7 +53,7 @@ void run(const char* name) {
   cudaFree(out); cudaFree(cyc);
 }
 int main() {
-  run<0>("ex2.f32");
+  run<0>("ex2.f32"); run<1>("ex2.f16x2"); run<2>("ex2.bf16x2"); run<12>("hadd2.f16x2"); run<13>("cvt.f16x2.f32"); run<14>("cvt.f32.f16");
   run<3>("ffma2 (x8/16)"); run<8>("fadd2 (x8/16)"); run<7>("ffma"); run<9>("fadd"); run<4>("fmnmx3"); run<5>("cvt.bf16x2"); run<10>("lop3"); run<11>("imad");
   printf("err=%s\n", cudaGetErrorString(cudaGetLastError()));
 }

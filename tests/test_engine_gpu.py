@@ -168,3 +168,17 @@ def test_graph_decode_equals_eager_and_oracle_cached_decode():
                 want.append(nxt)
                 logits = orc.decode_step_cached(sd, ospec, torch.tensor([nxt]), n + t, kc, vc, hooks)
         assert got_graph[b] == want, (b, got_graph[b], want)
+
+
+def test_run_rag_batch_equals_reference_loop_at_b1(engine32):
+    """Extension of SURVEY 8b: per-sample credibility in one packed batch == the reference's b = 1 loop."""
+    tok = synth.load_tokenizer()
+    rw = Re_Weighting_Strategy("tiny-llama", layers_to_be_modified={0: [1, 2], 1: [0, 3]}, tokenizer=tok, engine=engine32)
+    samples = [synth.nq_sample(seed, 3 + seed % 3, 20 + 7 * seed)[:3] for seed in range(4)]
+    qs, ps, ss = [s[0] for s in samples], [s[1] for s in samples], [s[2] for s in samples]
+    batched = rw.run_RAG_batch(qs, ps, ss, max_new_tokens=10)
+    for q, p, s, got in zip(qs, ps, ss, batched):
+        assert got == rw.run_RAG_batch([q], [p], [s], max_new_tokens=10)[0]
+    # and the public single-sample call is that same path (utils/re_weighting.py:115-138)
+    one = rw.run_RAG_with_attention_weighting(question=qs[0], paras=ps[0], scores=ss[0])
+    assert one[0] == batched[0][0] and one[1].startswith(batched[0][1])
