@@ -43,14 +43,6 @@ constexpr int kThreads = 384;
 constexpr int kTmemCols = 512;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
-// Exp phase in packed fp16: t - m is rounded to f16x2, one MUFU op (ex2.approx.f16x2) yields two probabilities
-// already in the packed layout of P, and the row sum is kept in f16x2 partials. Halves the MUFU work per key and
-// drops the fp32 -> 16-bit pack; P is then fp16 whatever the model dtype (the P V MMA takes A = f16, B = T).
-#ifndef CRAM_ATTN_EXP16
-#define CRAM_ATTN_EXP16 0
-#endif
-constexpr bool kExp16 = CRAM_ATTN_EXP16 != 0;
-
 // Debug timeline (scripts/trace_attn.py builds a separate library with -DCRAM_ATTN_TRACE=<block>; the product
 // build compiles none of this): clock64 stamps of one CTA's softmax warps, MMA issuer and producer, per tile.
 #ifdef CRAM_ATTN_TRACE
@@ -154,17 +146,6 @@ __device__ __forceinline__ uint32_t pack2<__half>(float lo, float hi) {
 // One K/V tile of one query row (= one thread): S from TMEM -> t = S*scale2 + bias[k] -> running max
 // (lazy rescale of O) -> P = 2^(t - m) packed to T and written back over the S columns.
 // kDiag: the tile straddles the causal diagonal, columns > climit are masked.
-__device__ __forceinline__ uint32_t ex2_h2(uint32_t x) {
-  uint32_t y;
-  asm("ex2.approx.f16x2 %0, %1;" : "=r"(y) : "r"(x));
-  return y;
-}
-__device__ __forceinline__ uint32_t hadd2(uint32_t a, uint32_t b) {
-  uint32_t r;
-  asm("add.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
-  return r;
-}
-
 template <typename T, int DH, bool kDiag>
 __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32_t o_addr, const uint32_t bias,
                                              const float scale2, const int climit, const bool first,
@@ -240,33 +221,6 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
   const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
   const uint64_t negm = pk2(-m_use, -m_use);
 
-  if (kExp16) {
-    uint32_t acc[4] = {0u, 0u, 0u, 0u};
-    uint32_t pk[32];
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-#pragma unroll
-      for (int i = 0; i < 32; i += 4) {
-        float e0, e1, e2, e3;
-        upk2(fadd2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), negm), e0, e1);
-        upk2(fadd2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), negm), e2, e3);
-        const uint32_t p01 = ex2_h2(pack2<__half>(e0, e1)), p23 = ex2_h2(pack2<__half>(e2, e3));
-        pk[c * 16 + i / 2 + 0] = p01;
-        pk[c * 16 + i / 2 + 1] = p23;
-        acc[(i >> 2) & 1] = hadd2(acc[(i >> 2) & 1], p01);
-        acc[2 + ((i >> 2) & 1)] = hadd2(acc[2 + ((i >> 2) & 1)], p23);
-      }
-    }
-    ptx::tmem_st32(s_addr, pk);
-    float sum = 0.f;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const __half2 h = *reinterpret_cast<const __half2*>(&acc[k]);
-      sum += __low2float(h) + __high2float(h);
-    }
-    l += sum;
-    return;
-  }
   uint64_t la = pk2(0.f, 0.f), lb = pk2(0.f, 0.f);
   uint32_t pk[32];
 #pragma unroll
@@ -319,8 +273,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
   constexpr int kSlabs = DH / 64;
   constexpr uint32_t kAbFmt = DType<T>::code == CRAM_BF16 ? 1u : 0u;
   constexpr uint32_t kIdescQK = ptx::umma_idesc_f16(kAbFmt, kBlockM, kBlockN, 0);
-  // with kExp16 the A operand of P V (P, in TMEM) is fp16 even for a bf16 model: a_format (bits 7-9) = 0
-  constexpr uint32_t kIdescPV = ptx::umma_idesc_f16(kAbFmt, kBlockM, DH, 1) & ~(kExp16 ? (kAbFmt << 7) : 0u);
+  constexpr uint32_t kIdescPV = ptx::umma_idesc_f16(kAbFmt, kBlockM, DH, 1);
 
   // ---- which tile pair ---------------------------------------------------------------------------
   const int head = blockIdx.x % p.n_heads;
