@@ -324,6 +324,26 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     }
     for (int i = 0; i < kBiasRing; ++i) ptx::mbar_init(&bar->bias_full[i], 1);
     ptx::fence_mbar_init();
+    // First loads (Q of both stages, K[0], K[1]) go out now: their HBM/L2 latency overlaps the TMEM allocation,
+    // the CTA-wide sync and the role dispatch instead of following them.
+#pragma unroll
+    for (int s = 0; s < kStages; ++s) {
+      if ((s ? n_t1 : n_t0) == 0) continue;
+      ptx::mbar_expect_tx(&bar->q_full[s], S::kQTileBytes);
+#pragma unroll
+      for (int sl = 0; sl < kSlabs; ++sl)
+        ptx::tma_load_2d(smem + S::kQ + s * S::kQTileBytes + sl * S::kQSlabBytes, &tmap_q, &bar->q_full[s],
+                         head * DH + sl * 64, q0 + (pair * kStages + s) * kBlockM);
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      if (j >= n_max) continue;
+      ptx::mbar_expect_tx(&bar->k_full[j], S::kTileBytes);
+#pragma unroll
+      for (int sl = 0; sl < kSlabs; ++sl)
+        ptx::tma_load_2d(smem + S::kK + j * S::kTileBytes + sl * S::kSlabBytes, &tmap_k, &bar->k_full[j],
+                         kv_head * DH + sl * 64, k0 + j * kBlockN);
+    }
   }
   if (warp == 9) ptx::tmem_alloc(tmem_ptr_smem, kTmemCols);
   ptx::tc_fence_before();
@@ -340,20 +360,9 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       // safe because slot j&7 is rewritten only after the V slot of tile j-6 was seen free.
       const bool biased = p.logcred != nullptr && ((p.head_mask >> head) & 1ull);
       const int bias_len = p.bias_len ? p.bias_len[seq] : len_k;
-      if (lane == 0) {
-#pragma unroll
-        for (int s = 0; s < kStages; ++s) {
-          if ((s ? n_t1 : n_t0) == 0) continue;
-          ptx::mbar_expect_tx(&bar->q_full[s], S::kQTileBytes);
-#pragma unroll
-          for (int sl = 0; sl < kSlabs; ++sl)
-            ptx::tma_load_2d(smem + S::kQ + s * S::kQTileBytes + sl * S::kQSlabBytes, &tmap_q, &bar->q_full[s],
-                             head * DH + sl * 64, q0 + (pair * kStages + s) * kBlockM);
-        }
-      }
       auto load_k_and_bias = [&](int j) {
         const int st = j % kKV;
-        if (lane == 0) {
+        if (lane == 0 && j >= 2) {  // K[0], K[1] were issued before the CTA-wide sync
           ptx::mbar_wait(&bar->k_empty[st], ((j / kKV) & 1) ^ 1);
           ptx::mbar_expect_tx(&bar->k_full[st], S::kTileBytes);
 #pragma unroll
