@@ -40,7 +40,10 @@ def run():
     lib.cram_debug_read_trace.argtypes = [ctypes.c_void_p]
     assert lib.cram_debug_read_trace(buf.ctypes.data) == 0
     t0 = buf[buf > 0].min()
-    for slot, name in ((0, "softmax stage0 (warp 0)"), (4, "softmax stage1 (warp 4)"), (8, "mma stage0"), (9, "mma stage1")):
+    slots = ((0, "softmax stage0 (warp 0)"), (4, "softmax stage1 (warp 4)"), (8, "mma stage0"), (9, "mma stage1"))
+    if os.environ.get("TRACE_SLOTS"):
+        slots = tuple((int(x), f"slot {x}") for x in os.environ["TRACE_SLOTS"].split(","))
+    for slot, name in slots:
         print(f"--- {name}: per tile [e0 rel start] d(e0->e1) d(e1->e2) d(e2->e3) | iteration period")
         prev = None
         for j in range(64):
