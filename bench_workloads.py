@@ -235,7 +235,9 @@ def run_decode(args):
     ms_token_step = ms_step / new
     model_gbs = (w_bytes + kv_step_bytes) / (ms_token_step / 1e3) / 1e9
     roofline = {"bound": "hbm", "kernel": "attn_decode_mma_kernel<bf16,128> (+combine when split)", "achieved": achieved,
-                "peak": hbm, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
+                "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+                # dram read + write bytes of one launch at this shape from ncu --set full (profiles/r1_decode_ncu_summary.md)
+                "traffic": 290.1e6 if (B, args.seq, ps, args.layers) == (64, 2048, 16, 0) else None, "traffic_unit": "bytes/launch",
                 "peak_source": f"{which} hbm_gbs (copy bandwidth)", "launch_ms": dec_avg_ms, "launches_timed": reps * spec.num_layers,
                 "bytes_per_launch": kv_bytes,
                 "timing": "CUDA events around replays of a graph holding the step's attention launches (all layers, real caches)",
