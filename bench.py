@@ -370,6 +370,40 @@ def run_ours(args):
                         "sample": f"oracle port, 2 of 32 layers x 1 sequence of {args.seq} tokens (hooked eager, bf16), "
                                   f"{ms_cpu:.0f} ms per sample, extrapolated x16"}
 
+    # ---- the reference's hooked eager attention executed by PyTorch on THIS GPU (context: the bar a user of the
+    # reference sees on a B200). One layer, one sequence: dense [1,H,T,T] mask rewrite
+    # (utils/re_weighting.py:36-61) + HF eager attention (modeling_llama.py:199-221), via the oracle's restatement.
+    ref_on_gpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            from oracle import cram_oracle as orc
+            T0 = int(lens[0])
+            gq = torch.randn(1, spec.num_heads, T0, spec.head_dim, device=dev).bfloat16()
+            gk = torch.randn(1, spec.num_kv_heads, T0, spec.head_dim, device=dev).bfloat16()
+            gv = torch.randn_like(gk)
+            base = torch.triu(torch.full((T0, T0), torch.finfo(torch.bfloat16).min, dtype=torch.bfloat16, device=dev), 1)[None, None]
+            lcg = torch.zeros(1, T0, dtype=torch.bfloat16, device=dev)
+            lcg[:, 16:T0 - 32] = -0.6931
+            hooked = list(range(28))
+
+            def ref_layer():
+                m = orc.edit_attention_mask(base, lcg, hooked, spec.num_heads, T0, T0, torch.bfloat16)
+                return orc.eager_attention(gq, gk, gv, m, spec.head_dim ** -0.5)
+
+            with torch.no_grad():
+                ref_layer(); torch.cuda.synchronize()
+                r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                r0.record()
+                for _ in range(3):
+                    ref_layer()
+                r1.record(); torch.cuda.synchronize()
+            ref_ms = r0.elapsed_time(r1) / 3
+            ref_on_gpu = {"what": "reference hook + HF eager attention through PyTorch on this GPU, one layer x one sequence (28 heads hooked)",
+                          "ms_per_layer_per_sequence": ref_ms, "ours_ms_per_layer_per_sequence": attn_avg_ms / args.batch,
+                          "ratio": ref_ms / (attn_avg_ms / args.batch) if attn_ms else None}
+        except Exception as e:  # context only: never fail the bench line on it
+            ref_on_gpu = {"error": repr(e)[:200]}
+
     # ---- IE sweep sub-measurement (the part that shards) ------------------------------------------------
     sweep = None
     if args.sweep_prompts > 0:
@@ -387,7 +421,8 @@ def run_ours(args):
                 "clocks": clocks.summary(),
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d_bytes,
                         "d2h_bytes_per_step": int(out_host.numel() * out_host.element_size())},
-                "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu_baseline, "sweep": sweep}
+                "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu_baseline,
+                "reference_attention_on_this_gpu": ref_on_gpu, "sweep": sweep}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
