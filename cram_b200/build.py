@@ -14,7 +14,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 BUILD_DIR = os.path.join(PKG_DIR, "_build")
 LIB_PATH = os.path.join(BUILD_DIR, "libcram_b200.so")
-SOURCES = ["capi.cu", "span_index.cu", "glue.cu", "attn_generic.cu", "attn_prefill_sm100.cu", "attn_decode.cu", "attn_decode_mma.cu"]
+SOURCES = ["capi.cu", "span_index.cu", "glue.cu", "attn_generic.cu", "attn_prefill_sm100.cu", "attn_decode.cu", "attn_decode_mma.cu", "linear_decode_sm100.cu"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-Xcompiler", "-fPIC",
               "--expt-relaxed-constexpr", "-Xptxas", "-v"]
 

@@ -229,6 +229,62 @@ __global__ void kv_append_kernel(const uint4* __restrict__ k, const uint4* __res
   }
 }
 
+// Rotary embedding + paged KV append in one pass over a fused QKV row (decode: one launch per layer instead of
+// two). Work item = (row, head, 16-byte vector j of the first half of the head): Q heads are rotated in place, K heads
+// are rotated in place AND written to the cache slot, V heads are copied to the cache slot. Same arithmetic as
+// rope_kernel (products rounded to T before the add, as torch does).
+template <typename T>
+__global__ void rope_kv_append_kernel(T* __restrict__ qkv, int64_t row_stride, int64_t n_rows, int n_heads, int n_kv_heads,
+                                      int head_dim, const T* __restrict__ cos_t, const T* __restrict__ sin_t,
+                                      const int32_t* __restrict__ positions, const int64_t* __restrict__ slot_mapping,
+                                      T* __restrict__ kc, T* __restrict__ vc, int64_t page_stride, int64_t token_stride,
+                                      int page_size) {
+  constexpr int N = Vec<T>::N;
+  const int half = head_dim / 2;
+  const int vec_per_head = half / N;
+  const int heads_all = n_heads + 2 * n_kv_heads;
+  const int64_t per_row = (int64_t)heads_all * vec_per_head;
+  const int64_t total = n_rows * per_row;
+  for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = idx / per_row;
+    const int rem = (int)(idx - r * per_row);
+    const int h = rem / vec_per_head;
+    const int j = (rem - h * vec_per_head) * N;
+    T* base = qkv + r * row_stride + (int64_t)h * head_dim;
+    Vec<T> x1 = ldvec(base + j), x2 = ldvec(base + j + half);
+    const int64_t slot = slot_mapping[r];
+    if (h >= n_heads + n_kv_heads) {  // V head: copy only
+      if (slot >= 0) {
+        T* dst = vc + (slot / page_size) * page_stride + (slot % page_size) * token_stride +
+                 (int64_t)(h - n_heads - n_kv_heads) * head_dim;
+        stvec(dst + j, x1);
+        stvec(dst + j + half, x2);
+      }
+      continue;
+    }
+    const int pos = positions[r];
+    Vec<T> c1 = ldvec(cos_t + (int64_t)pos * head_dim + j), c2 = ldvec(cos_t + (int64_t)pos * head_dim + j + half);
+    Vec<T> s1 = ldvec(sin_t + (int64_t)pos * head_dim + j), s2 = ldvec(sin_t + (int64_t)pos * head_dim + j + half);
+    Vec<T> o1, o2;
+#pragma unroll
+    for (int e = 0; e < N; ++e) {
+      const float a = DType<T>::to_f(x1.v[e]), b = DType<T>::to_f(x2.v[e]);
+      o1.v[e] = DType<T>::from_f(__fadd_rn(round_to<T>(__fmul_rn(a, DType<T>::to_f(c1.v[e]))),
+                                           round_to<T>(__fmul_rn(-b, DType<T>::to_f(s1.v[e])))));
+      o2.v[e] = DType<T>::from_f(__fadd_rn(round_to<T>(__fmul_rn(b, DType<T>::to_f(c2.v[e]))),
+                                           round_to<T>(__fmul_rn(a, DType<T>::to_f(s2.v[e])))));
+    }
+    stvec(base + j, o1);
+    stvec(base + j + half, o2);
+    if (h >= n_heads && slot >= 0) {
+      T* dst = kc + (slot / page_size) * page_stride + (slot % page_size) * token_stride + (int64_t)(h - n_heads) * head_dim;
+      stvec(dst + j, o1);
+      stvec(dst + j + half, o2);
+    }
+  }
+}
+
 static inline int stream_grid(int64_t work_items, int threads) {
   int64_t b = (work_items + threads - 1) / threads;
   int64_t cap = (int64_t)sm_count() * 16;  // multiple of the SM count; grid-stride covers the rest
@@ -278,6 +334,25 @@ extern "C" int cram_rope(void* qk, int64_t row_stride, int64_t n_rows, int n_rot
                             (T*)qk, row_stride, n_rows, n_rot_heads, head_dim, (const T*)cos_table,
                             (const T*)sin_table, positions)));
   return check_launch("rope_kernel");
+}
+
+extern "C" int cram_rope_kv_append(void* qkv, int64_t row_stride, int64_t n_rows, int n_heads, int n_kv_heads, int head_dim,
+                                   const void* cos_table, const void* sin_table, const int32_t* positions,
+                                   const int64_t* slot_mapping, void* k_cache, void* v_cache, int64_t page_stride,
+                                   int64_t token_stride, int page_size, int dtype, cram_stream_t stream) {
+  CRAM_REQUIRE(n_rows >= 0 && n_heads > 0 && n_kv_heads > 0 && head_dim > 0 && page_size > 0, "cram_rope_kv_append: bad shape");
+  if (n_rows == 0) return CRAM_OK;
+  const int vec = 16 / (int)dtype_size(dtype);
+  CRAM_REQUIRE((head_dim / 2) % vec == 0 && row_stride % vec == 0 && page_stride % vec == 0 && token_stride % vec == 0,
+               "cram_rope_kv_append: head_dim/2 and strides must be multiples of %d", vec);
+  CRAM_REQUIRE(aligned16(qkv) && aligned16(cos_table) && aligned16(sin_table) && aligned16(k_cache) && aligned16(v_cache),
+               "cram_rope_kv_append: pointers must be 16-byte aligned");
+  const int64_t items = n_rows * (n_heads + 2 * n_kv_heads) * (head_dim / 2 / vec);
+  DISPATCH_DTYPE(dtype, (rope_kv_append_kernel<T><<<stream_grid(items, 256), 256, 0, (cudaStream_t)stream>>>(
+                            (T*)qkv, row_stride, n_rows, n_heads, n_kv_heads, head_dim, (const T*)cos_table,
+                            (const T*)sin_table, positions, slot_mapping, (T*)k_cache, (T*)v_cache, page_stride,
+                            token_stride, page_size)));
+  return check_launch("rope_kv_append_kernel");
 }
 
 extern "C" int cram_silu_mul(const void* gate_up, void* out, int64_t n_rows, int inter, int dtype,

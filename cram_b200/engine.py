@@ -150,11 +150,18 @@ class CramEngine:
         self._rope_len = n_pos
 
     # ---- layer pieces -------------------------------------------------------------------------------
-    def _qkv(self, l: int, x: torch.Tensor, pending: Optional[torch.Tensor], positions: torch.Tensor) -> torch.Tensor:
+    def _qkv(self, l: int, x: torch.Tensor, pending: Optional[torch.Tensor], positions: torch.Tensor,
+             kv: Optional["PagedKV"] = None, slot_mapping: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Input norm (+ pending residual), fused QKV projection, rotary embedding; with `kv`, the rotated K and V
+        rows also go to their cache slots in the same launch as the rotation."""
         s = self.spec
         h = ops.rmsnorm(x, self.w[f"in_norm.{l}"], s.rms_eps, residual=pending)  # x += pending (in place)
         qkv = F.linear(h, self.w[f"wqkv.{l}"], self.w.get(f"bqkv.{l}"))
-        ops.rope_(qkv, s.num_heads + s.num_kv_heads, s.head_dim, self.cos, self.sin, positions)
+        if kv is None:
+            ops.rope_(qkv, s.num_heads + s.num_kv_heads, s.head_dim, self.cos, self.sin, positions)
+        else:
+            ops.rope_kv_append_(qkv, s.num_heads, s.num_kv_heads, s.head_dim, self.cos, self.sin, positions, slot_mapping,
+                                kv.k[l], kv.v[l])
         return qkv
 
     def split_qkv(self, qkv: torch.Tensor):
@@ -186,10 +193,8 @@ class CramEngine:
         x = F.embedding(input_ids, self.w["embed"])
         pending = None
         for l in range(s.num_layers):
-            qkv = self._qkv(l, x, pending, positions)
+            qkv = self._qkv(l, x, pending, positions, kv, slot_mapping)
             q, k, v = self.split_qkv(qkv)
-            if kv is not None:
-                ops.kv_append(k, v, slot_mapping, kv.k[l], kv.v[l], s.num_kv_heads, s.head_dim)
             mask = int(head_masks[l]) if (head_masks is not None and logcred is not None) else 0
             attn = ops.attn_prefill(q, k, v, cu_seqlens, max_seqlen, s.num_heads, s.num_kv_heads, s.head_dim,
                                     logcred=logcred, head_mask=mask, kernel=attn_kernel)
@@ -236,9 +241,8 @@ class CramEngine:
         x = F.embedding(tokens, self.w["embed"])
         pending = None
         for l in range(s.num_layers):
-            qkv = self._qkv(l, x, pending, positions)
+            qkv = self._qkv(l, x, pending, positions, kv, slot)
             q, k, v = self.split_qkv(qkv)
-            ops.kv_append(k, v, slot, kv.k[l], kv.v[l], s.num_kv_heads, s.head_dim)
             mask = int(head_masks[l]) if (head_masks is not None and logcred is not None) else 0
             attn = ops.attn_decode(q, kv.k[l], kv.v[l], block_table, seqlens, max_seqlen, s.num_heads, s.num_kv_heads,
                                    s.head_dim, logcred=logcred, head_mask=mask, bias_len=bias_len, workspace=workspace)

@@ -199,6 +199,61 @@ def kv_append(k: torch.Tensor, v: torch.Tensor, slot_mapping: torch.Tensor, k_ca
     launch_count += 1
 
 
+def rope_kv_append_(qkv: torch.Tensor, n_heads: int, n_kv_heads: int, head_dim: int, cos: torch.Tensor, sin: torch.Tensor,
+                    positions: torch.Tensor, slot_mapping: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor) -> None:
+    """rope_ on the Q and K heads of the fused QKV rows, then kv_append of rotated K and V, in ONE launch."""
+    global launch_count
+    lib = _lib.load()
+    _cuda(qkv, "qkv")
+    assert qkv.dim() == 2 and qkv.stride(1) == 1 and positions.dtype == torch.int32 and slot_mapping.dtype == torch.int64
+    assert cos.is_contiguous() and sin.is_contiguous() and cos.dtype == qkv.dtype and cos.shape[1] == head_dim
+    assert k_cache.dtype == qkv.dtype and k_cache.stride() == v_cache.stride()
+    check(lib.cram_rope_kv_append(_ptr(qkv), qkv.stride(0), qkv.shape[0], n_heads, n_kv_heads, head_dim, _ptr(cos), _ptr(sin),
+                                  _ptr(positions), _ptr(slot_mapping), _ptr(k_cache), _ptr(v_cache), k_cache.stride(0),
+                                  k_cache.stride(1), k_cache.shape[1], dtype_code(qkv.dtype), _stream()),
+          "cram_rope_kv_append")
+    launch_count += 1
+
+
+LINEAR_PLAIN, LINEAR_RESIDUAL, LINEAR_SWIGLU = 0, 1, 2
+_linear_ws: dict = {}
+
+
+def linear_decode_workspace(n_out: int, k: int, mode: int, device) -> torch.Tensor:
+    """One zero-initialised workspace per device, grown to the largest request (launches are stream-ordered)."""
+    need = int(_lib.load().cram_linear_decode_workspace_bytes(n_out, k, mode))
+    ws = _linear_ws.get(str(device))
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(max(need, 1 << 24), dtype=torch.uint8, device=device)
+        _linear_ws[str(device)] = ws
+    return ws
+
+
+def linear_decode(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, mode: int = LINEAR_PLAIN,
+                  out: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Decode-step projection of <= 64 rows (cram_linear_decode). mode LINEAR_PLAIN: x @ w.T (+ bias);
+    LINEAR_RESIDUAL: out += x @ w.T in place (out is the residual stream); LINEAR_SWIGLU: w = [gate; up] rows,
+    returns silu(x @ gate.T) * (x @ up.T)."""
+    global launch_count
+    lib = _lib.load()
+    _cuda(x, "x")
+    assert x.dim() == 2 and w.dim() == 2 and x.stride(1) == 1 and w.stride(1) == 1 and x.dtype == w.dtype
+    m, k = x.shape
+    n_out = w.shape[0] // 2 if mode == LINEAR_SWIGLU else w.shape[0]
+    assert w.shape[1] == k
+    if out is None:
+        assert mode != LINEAR_RESIDUAL, "LINEAR_RESIDUAL adds into `out`"
+        out = torch.empty((m, n_out), dtype=x.dtype, device=x.device)
+    assert out.shape == (m, n_out) and out.stride(1) == 1 and out.dtype == x.dtype
+    if workspace is None:
+        workspace = linear_decode_workspace(n_out, k, mode, x.device)
+    check(lib.cram_linear_decode(_ptr(x), x.stride(0), m, _ptr(w), w.stride(0), n_out, k, _ptr(bias), _ptr(out),
+                                 out.stride(0), mode, dtype_code(x.dtype), _ptr(workspace), workspace.numel(), _stream()),
+          "cram_linear_decode")
+    launch_count += 1
+    return out
+
+
 # ------------------------------------------------------------------------------------------------
 def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: Optional[torch.Tensor] = None,
             out: Optional[torch.Tensor] = None) -> torch.Tensor:

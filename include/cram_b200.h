@@ -180,6 +180,23 @@ int cram_rmsnorm(void* x, const void* residual, const void* weight, void* out, i
 int cram_rope(void* qk, int64_t row_stride, int64_t n_rows, int n_rot_heads, int head_dim,
               const void* cos_table, const void* sin_table, const int32_t* positions, int dtype,
               cram_stream_t stream);
+/* cram_rope on the Q and K heads of a fused [.., (n_heads + 2 n_kv_heads) * head_dim] row AND cram_kv_append of
+ * the rotated K and of V, in one launch (the decode step's per-layer glue). */
+int cram_rope_kv_append(void* qkv, int64_t row_stride, int64_t n_rows, int n_heads, int n_kv_heads, int head_dim,
+                        const void* cos_table, const void* sin_table, const int32_t* positions,
+                        const int64_t* slot_mapping, void* k_cache, void* v_cache, int64_t page_stride,
+                        int64_t token_stride, int page_size, int dtype, cram_stream_t stream);
+/* Decode-step projection (<= 64 token rows) with the step's glue fused in; streams w once (HBM-bound).
+ *   mode 0: y[m, n] = sum_k x[m,k] w[n,k] (+ bias[n])        w = [n_out, k]
+ *   mode 1: y[m, n] += T(sum_k x[m,k] w[n,k])                 the residual add of o_proj / down_proj, in place
+ *   mode 2: y[m, n] = T(T(silu(T(g))) * T(u)), g = x . w[n], u = x . w[n_out + n]     w = [2 n_out, k] (gate, up):
+ *           LlamaMLP act_fn(gate_proj(x)) * up_proj(x) (transformers modeling_llama.py LlamaMLP.forward)
+ * bf16 / fp16; k and the row strides multiples of 8; workspace from cram_linear_decode_workspace_bytes, its first
+ * 16 KB zeroed once by the caller (ticket counters; every launch leaves them zero). */
+size_t cram_linear_decode_workspace_bytes(int n_out, int k, int mode);
+int cram_linear_decode(const void* x, int64_t ldx, int m, const void* w, int64_t ldw, int n_out, int k,
+                       const void* bias, void* y, int64_t ldy, int mode, int dtype, void* workspace,
+                       size_t workspace_bytes, cram_stream_t stream);
 /* out[r, j] = silu(gate_up[r, j]) * gate_up[r, inter + j] */
 int cram_silu_mul(const void* gate_up, void* out, int64_t n_rows, int inter, int dtype, cram_stream_t stream);
 

@@ -48,6 +48,29 @@ def test_rope_matches_hf(dtype):
     assert torch.equal(got, want)  # same three roundings as HF -> bit-exact
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("page_size", [16, 5])
+def test_fused_rope_kv_append_equals_the_two_kernels(dtype, page_size):
+    torch.manual_seed(2)
+    H, Hkv, dh, N, n_pages = 7, 1, 128, 131, 40
+    qkv = torch.randn(N, (H + 2 * Hkv) * dh, device=DEV).to(dtype)
+    pos = torch.randint(0, 500, (N,), device=DEV, dtype=torch.int32)
+    spec = orc.ModelSpec(1, H, Hkv, dh, 64, 64, 10, rope_theta=10000.0)
+    cos_t, sin_t = orc.rope_cos_sin(spec, torch.arange(512)[None], dtype)
+    cos_t, sin_t = cos_t[0].to(DEV).contiguous(), sin_t[0].to(DEV).contiguous()
+    slot = torch.randperm(n_pages * page_size, device=DEV)[:N].to(torch.int64)
+    slot[3] = -1  # a skipped row: rotated in place, not stored
+    shape = (n_pages, page_size, Hkv, dh)
+    kc0, vc0 = torch.randn(shape, device=DEV).to(dtype), torch.randn(shape, device=DEV).to(dtype)
+    want, kc_w, vc_w = qkv.clone(), kc0.clone(), vc0.clone()
+    ops.rope_(want, H + Hkv, dh, cos_t, sin_t, pos)
+    ops.kv_append(want[:, H * dh:(H + Hkv) * dh], want[:, (H + Hkv) * dh:], slot, kc_w, vc_w, Hkv, dh)
+    got, kc_g, vc_g = qkv.clone(), kc0.clone(), vc0.clone()
+    ops.rope_kv_append_(got, H, Hkv, dh, cos_t, sin_t, pos, slot, kc_g, vc_g)
+    assert torch.equal(got, want) and torch.equal(kc_g, kc_w) and torch.equal(vc_g, vc_w)
+    assert not torch.equal(kc_g, kc0)
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_silu_mul(dtype):
     torch.manual_seed(2)
