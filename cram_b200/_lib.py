@@ -76,9 +76,8 @@ SIGNATURES = {
     "cram_rmsnorm": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_int, C.c_float, C.c_int, vp]),
     "cram_rope": (C.c_int, [vp, C.c_int64, C.c_int64, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp]),
     "cram_silu_mul": (C.c_int, [vp, vp, C.c_int64, C.c_int, C.c_int, vp]),
-    "cram_linear_decode_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "cram_linear_decode": (C.c_int, [vp, C.c_int64, C.c_int, vp, C.c_int64, C.c_int, C.c_int, vp, vp, C.c_int64, C.c_int,
-                                     C.c_int, vp, C.c_size_t, vp]),
+                                     C.c_int, vp]),
     "cram_rope_kv_append": (C.c_int, [vp, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp,
                                       C.c_int64, C.c_int64, C.c_int, C.c_int, vp]),
     "cram_rank_heads": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp]),

@@ -9,9 +9,13 @@
 //     in 64 TMEM columns;
 //   * one producer lane feeds a 4-stage ring with TMA (16 KB of weights + 8 KB of x per 64-wide K block; x rows
 //     beyond m are zero-filled by the tensor map), one elected lane issues the MMAs, tcgen05.commit frees ring slots;
-//   * 2 CTAs per SM (2 x 96 KB of ring = 128 KB of weights in flight per SM); grid = weight tiles x split-K, the
-//     split chosen on the host so that the grid fills 2 x #SM slots; split-K partials go through an fp32
-//     workspace and the LAST CTA of a tile (atomic ticket) sums them in split order -- deterministic;
+//   * 2 CTAs per SM (2 x 96 KB of ring = 128 KB of weights in flight per SM);
+//   * split-K across a thread-block CLUSTER (2, 4 or 8 CTAs share a weight tile, each streams a K range): the
+//     partial accumulators are reduce-scattered through distributed shared memory -- CTA j receives everybody's
+//     token rows [j*64/split, (j+1)*64/split), sums them in rank order (deterministic) and runs the epilogue for
+//     those rows. No global workspace, no atomics, no second kernel;
+//   * programmatic dependent launch: the weights do not depend on the previous kernel, so the first ring of W
+//     tiles is requested before griddepcontrol.wait; only x (and y) wait for the dependency;
 //   * epilogues: 0 = (+ bias) -> y; 1 = y += T(acc) (the residual add of o_proj / down_proj, in place);
 //     2 = SwiGLU: the tile holds 64 gate rows and their 64 up rows, out = T(T(silu(T(gate))) * T(up)) -- the
 //     roundings of cram_silu_mul / HF eager.
@@ -33,32 +37,155 @@ constexpr int kXBytes = kRows * kBlockK * 2;   // 8 KB
 constexpr int kStageBytes = kWBytes + kXBytes;
 constexpr int kThreads = 192;  // warps 0-3 epilogue, warp 4 producer, warp 5 MMA issuer / TMEM owner
 constexpr int kTmemCols = 64;
-constexpr int kMaxTiles = 4096;
 constexpr uint32_t kDescHi = ptx::umma_desc_hi(1024);
 
 struct Bars {
   uint64_t full[kRing], empty[kRing];
   uint64_t acc_full;
   uint32_t tmem_ptr;
-  int is_last;
 };
 constexpr int kSmemRequest = kRing * kStageBytes + (int)sizeof(Bars) + 1024;
+static_assert(kTileN * kRows * 4 <= kRing * kStageBytes, "the reduce-scatter buffer reuses the drained ring");
+
+// Debug timeline (scripts/profile_linear.py trace builds a separate library with -DCRAM_LINEAR_TRACE; the product
+// build compiles none of this): %globaltimer stamps of every CTA of the last 32 launches.
+#ifdef CRAM_LINEAR_TRACE
+__device__ unsigned long long g_lin_trace[32][320][8];
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define LIN_TRACE(e)                                                                         \
+  do {                                                                                       \
+    if (blockIdx.x < 320) g_lin_trace[p.trace_slot & 31][blockIdx.x][e] = gtime();           \
+  } while (0)
+#else
+#define LIN_TRACE(e) \
+  do {               \
+  } while (0)
+#endif
 
 struct Params {
+  int trace_slot;
   void* y;
   int64_t ldy;
   const void* bias;
   int m, n_out, k_blocks, split;
   int up_row0;  // mode 2: first up row (= n_out)
-  float* partials;
-  int* counters;
 };
 
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+// all threads of all CTAs of the cluster
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// shared::cluster address of `local_addr` (a shared::cta address of this CTA) inside CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t local_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_v4(uint32_t addr, float a, float b, float c, float d) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 
 template <typename T>
 __device__ __forceinline__ float rnd(float v) {
   return DType<T>::to_f(DType<T>::from_f(v));
+}
+
+// What the epilogue of weight row n needs from global memory besides the accumulator -- the bias (mode 0) or the
+// residual values it adds to (mode 1) -- requested early, so that the latency hides behind the main loop.
+template <typename T, int kMode, int kCount>
+__device__ __forceinline__ void load_pre(const Params& p, int n, int m0, float (&pre)[kCount]) {
+  if (n >= p.n_out) return;
+  if (kMode == 0) {
+    pre[0] = p.bias ? DType<T>::to_f(reinterpret_cast<const T*>(p.bias)[n]) : 0.f;
+  } else if (kMode == 1) {
+    const T* y = reinterpret_cast<const T*>(p.y);
+#pragma unroll
+    for (int i = 0; i < kCount; ++i) pre[i] = m0 + i < p.m ? DType<T>::to_f(y[(int64_t)(m0 + i) * p.ldy + n]) : 0.f;
+  }
+}
+
+// Epilogue of one weight row n for kCount token rows starting at m0 (v[i]: fp32 sums; up[i]: mode 2 only).
+template <typename T, int kMode, int kCount>
+__device__ __forceinline__ void store_rows(const Params& p, int n, int m0, const float (&v)[kCount], const float (&up)[kCount],
+                                           const float (&pre)[kCount]) {
+  if (n >= p.n_out) return;
+  T* y = reinterpret_cast<T*>(p.y);
+#pragma unroll
+  for (int i = 0; i < kCount; ++i) {
+    if (m0 + i < p.m) {
+      float r;
+      if (kMode == 0) {
+        r = v[i] + pre[0];
+      } else if (kMode == 1) {
+        r = pre[i] + rnd<T>(v[i]);
+      } else {
+        const float g = rnd<T>(v[i]);
+        r = rnd<T>(g / (1.0f + expf(-g))) * rnd<T>(up[i]);
+      }
+      y[(int64_t)(m0 + i) * p.ldy + n] = DType<T>::from_f(r);
+    }
+  }
+}
+
+// Split-K over a cluster of kSplit CTAs: reduce-scatter of the [128 x 64] fp32 partial tiles through distributed
+// shared memory. `recv` is this CTA's drained ring, as float4 [source rank][kMS / 4][weight row] (lane-contiguous).
+template <typename T, int kMode, int kSplit>
+__device__ __forceinline__ void cluster_reduce_and_store(const Params& p, const float (&acc)[kRows], uint8_t* recv, int tile,
+                                                         int nl, bool epilogue_thread) {
+  constexpr int kMS = kRows / kSplit;  // token rows per CTA after the scatter
+  constexpr int kQ = kMS / 4;
+  const uint32_t rank = cluster_ctarank();
+  const int n = kMode == 2 ? tile * 64 + nl : tile * kTileN + nl;
+  const bool owner = epilogue_thread && (kMode != 2 || nl < 64);
+  float pre[kMS];
+  if (owner) load_pre<T, kMode, kMS>(p, n, (int)rank * kMS, pre);
+  cluster_sync();  // every CTA of the cluster has drained its ring: the rings may now be overwritten remotely
+  if (epilogue_thread) {
+    const uint32_t mine = ptx::smem_u32(recv) + ((rank * kQ) * kTileN + nl) * 16;
+#pragma unroll
+    for (int j = 0; j < kSplit; ++j) {
+      const uint32_t dst = map_to_cta(mine, (uint32_t)j);
+#pragma unroll
+      for (int q = 0; q < kQ; ++q)
+        st_cluster_v4(dst + q * kTileN * 16, acc[j * kMS + 4 * q], acc[j * kMS + 4 * q + 1], acc[j * kMS + 4 * q + 2],
+                      acc[j * kMS + 4 * q + 3]);
+    }
+  }
+  cluster_sync();  // all partial rows of this CTA's token slice have landed
+#ifdef CRAM_LINEAR_TRACE
+  if (threadIdx.x == 0) LIN_TRACE(6);
+#endif
+  if (!owner) return;
+  const float4* r = reinterpret_cast<const float4*>(recv);
+  auto sum_row = [&](int row, float (&out)[kMS]) {
+#pragma unroll
+    for (int e = 0; e < kMS; ++e) out[e] = 0.f;
+#pragma unroll
+    for (int s = 0; s < kSplit; ++s) {  // rank order: the sum does not depend on timing
+#pragma unroll
+      for (int q = 0; q < kQ; ++q) {
+        const float4 v = r[(s * kQ + q) * kTileN + row];
+        out[4 * q] += v.x;
+        out[4 * q + 1] += v.y;
+        out[4 * q + 2] += v.z;
+        out[4 * q + 3] += v.w;
+      }
+    }
+  };
+  float v[kMS], up[kMS];
+  sum_row(nl, v);
+  if (kMode == 2) sum_row(nl + 64, up);
+  store_rows<T, kMode, kMS>(p, n, (int)rank * kMS, v, kMode == 2 ? up : v, pre);
 }
 
 template <typename T, int kMode>
@@ -69,15 +196,17 @@ linear_decode_sm100_kernel(const __grid_constant__ CUtensorMap tmap_w, const __g
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   Bars* bar = reinterpret_cast<Bars*>(smem + kRing * kStageBytes);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // grid = tiles x split, the `split` CTAs of a tile are consecutive (= one cluster)
   const int tile = blockIdx.x / p.split, sp = blockIdx.x - tile * p.split;
-  // K blocks [kb0, kb1) of this split: the first `rem` splits take one more
+  // K blocks [kb0, kb0 + n_kb) of this split: the first `rem` splits take one more
   const int per = p.k_blocks / p.split, rem = p.k_blocks - per * p.split;
   const int kb0 = sp * per + min(sp, rem), n_kb = per + (sp < rem ? 1 : 0);
-  // weight row of TMEM lane 0 / of lane 64 (mode 2: gate rows then their up rows)
+  // weight row of TMEM lane 0 / of lane 64 (mode 2: gate rows, then their up rows)
   const int row_lo = kMode == 2 ? tile * 64 : tile * kTileN;
   const int row_hi = kMode == 2 ? p.up_row0 + tile * 64 : tile * kTileN + 64;
 
   if (warp == 4 && lane == 0) {
+    LIN_TRACE(0);
     ptx::prefetch_tmap(&tmap_w);
     ptx::prefetch_tmap(&tmap_x);
     for (int i = 0; i < kRing; ++i) {
@@ -103,8 +232,13 @@ linear_decode_sm100_kernel(const __grid_constant__ CUtensorMap tmap_w, const __g
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = bar->tmem_ptr;
-  ptx::griddep_wait();  // x, y, the split-K workspace: everything below may depend on the previous kernel
+  if (threadIdx.x == 0) LIN_TRACE(1);
+  ptx::griddep_wait();  // x and y: everything below may depend on the previous kernel
+  if (threadIdx.x == 0) LIN_TRACE(2);
 
+  float acc[kRows];
+  float pre[kRows];  // split == 1: bias / residual values requested before the main loop ends
+  const int nl = (warp & 3) * 32 + lane;  // epilogue warps: TMEM lane = weight row inside the tile
   if (warp == 4) {
     if (lane == 0) {
       for (int i = 0; i < n_kb && i < kRing; ++i)
@@ -120,6 +254,7 @@ linear_decode_sm100_kernel(const __grid_constant__ CUtensorMap tmap_w, const __g
         ptx::tma_load_2d(w_dst + kWBytes, &tmap_x, &bar->full[st], kc, 0);
       }
     }
+    __syncwarp();
   } else if (warp == 5) {
     if (ptx::elect_one_sync()) {
       constexpr uint32_t kAbFmt = DType<T>::code == CRAM_BF16 ? 1u : 0u;
@@ -129,6 +264,7 @@ linear_decode_sm100_kernel(const __grid_constant__ CUtensorMap tmap_w, const __g
       for (int i = 0; i < n_kb; ++i) {
         const int st = i % kRing;
         ptx::mbar_wait(&bar->full[st], (i / kRing) & 1);
+        if (i == 0) LIN_TRACE(3);
         ptx::tc_fence_after();
         const uint32_t a = w_lo + st * (kStageBytes >> 4), b = x_lo + st * (kStageBytes >> 4);
         ptx::mma_ss_imm<kDescHi, 0, 0, 0>(tmem, a, b, kIdesc, i > 0 ? 1u : 0u);
@@ -138,11 +274,12 @@ linear_decode_sm100_kernel(const __grid_constant__ CUtensorMap tmap_w, const __g
         ptx::tc_commit(&bar->empty[st]);
       }
       ptx::tc_commit(&bar->acc_full);
+      LIN_TRACE(4);
     }
+    __syncwarp();
   } else {
-    // ============================== epilogue (warps 0-3, TMEM lanes 32w..32w+31) ======================
-    const int nl = warp * 32 + lane;  // TMEM lane = weight row inside the tile
-    float acc[kRows];
+    // ============================== accumulator -> registers (warps 0-3, TMEM lanes 32w..32w+31) =======
+    if (kMode != 2 && p.split == 1) load_pre<T, kMode, kRows>(p, tile * kTileN + nl, 0, pre);
     if (n_kb > 0) {
       ptx::mbar_wait(&bar->acc_full, 0);
       ptx::tc_fence_after();
@@ -156,90 +293,55 @@ linear_decode_sm100_kernel(const __grid_constant__ CUtensorMap tmap_w, const __g
         acc[i] = __uint_as_float(r0[i]);
         acc[32 + i] = __uint_as_float(r1[i]);
       }
+      if (threadIdx.x == 0) LIN_TRACE(5);
     } else {
 #pragma unroll
       for (int i = 0; i < kRows; ++i) acc[i] = 0.f;
     }
-    bool finish = true;
-    if (p.split > 1) {
-      // partial tile layout [m / 4][weight row][4]: consecutive lanes write consecutive 16-byte pieces
-      float4* mine = reinterpret_cast<float4*>(p.partials + (int64_t)blockIdx.x * kTileN * kRows) + nl;
+  }
+
+  if (p.split > 1) {
+    // every thread of the cluster takes part in the two cluster barriers inside
+    if (p.split == 2) cluster_reduce_and_store<T, kMode, 2>(p, acc, smem, tile, nl, warp < 4);
+    else if (p.split == 4) cluster_reduce_and_store<T, kMode, 4>(p, acc, smem, tile, nl, warp < 4);
+    else cluster_reduce_and_store<T, kMode, 8>(p, acc, smem, tile, nl, warp < 4);
+  } else if (warp < 4) {
+    if (kMode == 2) {
+      // lanes 0-63 hold gate rows, lanes 64-127 their up rows. Gate threads finish token rows 0-31 of their weight
+      // row, up threads rows 32-63: each side hands the other the half it needs through the drained ring.
+      float* s_up = reinterpret_cast<float*>(smem);            // [32 token rows][64]: up values, rows 0-31
+      float* s_gate = reinterpret_cast<float*>(smem) + 32 * 64;  // [32 token rows][64]: gate values, rows 32-63
+      const int row = nl & 63;
+      if (nl >= 64) {
 #pragma unroll
-      for (int i = 0; i < kRows / 4; ++i)
-        __stcg(mine + i * kTileN, make_float4(acc[4 * i], acc[4 * i + 1], acc[4 * i + 2], acc[4 * i + 3]));
-      __threadfence();
-      epi_bar();
-      if (threadIdx.x == 0) {
-        const int ticket = atomicAdd(p.counters + tile, 1);
-        bar->is_last = ticket == p.split - 1;
-        if (ticket == p.split - 1) p.counters[tile] = 0;  // ready for the next launch (stream order)
+        for (int m = 0; m < 32; ++m) s_up[m * 64 + row] = acc[m];
+      } else {
+#pragma unroll
+        for (int m = 0; m < 32; ++m) s_gate[m * 64 + row] = acc[32 + m];
       }
       epi_bar();
-      finish = bar->is_last != 0;
-      if (finish) {
-        __threadfence();
+      float g[32], u[32];
+      if (nl >= 64) {
 #pragma unroll
-        for (int i = 0; i < kRows; ++i) acc[i] = 0.f;
-        for (int s = 0; s < p.split; ++s) {  // fixed order: the sum does not depend on which CTA came last
-          const float4* src =
-              reinterpret_cast<const float4*>(p.partials + ((int64_t)tile * p.split + s) * kTileN * kRows) + nl;
-#pragma unroll
-          for (int i = 0; i < kRows / 4; ++i) {
-            const float4 v = __ldcg(src + i * kTileN);
-            acc[4 * i] += v.x;
-            acc[4 * i + 1] += v.y;
-            acc[4 * i + 2] += v.z;
-            acc[4 * i + 3] += v.w;
-          }
-        }
-      }
-    }
-    if (finish) {
-      T* y = reinterpret_cast<T*>(p.y);
-      if (kMode == 2) {
-        // lanes 64-127 hold the up rows of the gate rows in lanes 0-63: hand them over through the (now idle) ring
-        T* s_up = reinterpret_cast<T*>(smem);  // [m][64]
-        if (nl >= 64) {
-#pragma unroll
-          for (int m = 0; m < kRows; ++m) s_up[m * 64 + (nl - 64)] = DType<T>::from_f(acc[m]);
-        }
-        epi_bar();
-        const int n = tile * 64 + nl;
-        if (nl < 64 && n < p.n_out) {
-#pragma unroll
-          for (int m = 0; m < kRows; ++m) {
-            if (m < p.m) {
-              const float g = rnd<T>(acc[m]);
-              const float s = rnd<T>(g / (1.0f + expf(-g)));
-              y[(int64_t)m * p.ldy + n] = DType<T>::from_f(s * DType<T>::to_f(s_up[m * 64 + nl]));
-            }
-          }
+        for (int m = 0; m < 32; ++m) {
+          g[m] = s_gate[m * 64 + row];
+          u[m] = acc[32 + m];
         }
       } else {
-        const int n = tile * kTileN + nl;
-        if (n < p.n_out) {
-          const float b = (kMode == 0 && p.bias) ? DType<T>::to_f(reinterpret_cast<const T*>(p.bias)[n]) : 0.f;
-          if (kMode == 1) {
 #pragma unroll
-            for (int m0 = 0; m0 < kRows; m0 += 16) {  // 16 loads in flight, then their 16 stores
-              float res[16];
-#pragma unroll
-              for (int i = 0; i < 16; ++i) res[i] = m0 + i < p.m ? DType<T>::to_f(y[(int64_t)(m0 + i) * p.ldy + n]) : 0.f;
-#pragma unroll
-              for (int i = 0; i < 16; ++i)
-                if (m0 + i < p.m) y[(int64_t)(m0 + i) * p.ldy + n] = DType<T>::from_f(res[i] + rnd<T>(acc[m0 + i]));
-            }
-          } else {
-#pragma unroll
-            for (int m = 0; m < kRows; ++m)
-              if (m < p.m) y[(int64_t)m * p.ldy + n] = DType<T>::from_f(acc[m] + b);
-          }
+        for (int m = 0; m < 32; ++m) {
+          g[m] = acc[m];
+          u[m] = s_up[m * 64 + row];
         }
       }
+      store_rows<T, kMode, 32>(p, tile * 64 + row, nl >= 64 ? 32 : 0, g, u, g);
+    } else {
+      store_rows<T, kMode, kRows>(p, tile * kTileN + nl, 0, acc, acc, pre);
     }
   }
   ptx::tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) LIN_TRACE(7);
   if (warp == 5) ptx::tmem_dealloc(tmem, kTmemCols);
 }
 
@@ -285,46 +387,70 @@ int tmap_rows_by_k(CUtensorMap* m, const void* base, int dtype, int64_t rows, in
 
 inline int tiles_of(int n_out, int mode) { return mode == 2 ? (n_out + 63) / 64 : (n_out + kTileN - 1) / kTileN; }
 
-// split-K factor: fill the 2 x #SM CTA slots in as few waves as possible; a CTA costs ~4 K-blocks of start-up /
-// epilogue latency and the reducing CTA reads `split` partial tiles.
-int g_pdl = 1;          // programmatic dependent launch on (cram_debug_linear_pdl switches it off for A/B timing)
+int g_pdl = 1;          // programmatic dependent launch (cram_debug_linear_pdl switches it off for A/B timing)
 int g_force_split = 0;  // scripts/profile_linear.py only (cram_debug_linear_split)
+
+void fill_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid, int split, cudaStream_t stream) {
+  cfg->gridDim = dim3((unsigned)grid);
+  cfg->blockDim = dim3(kThreads);
+  cfg->dynamicSmemBytes = kSmemRequest;
+  cfg->stream = stream;
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // see griddep_wait in the kernel
+  attr[0].val.programmaticStreamSerializationAllowed = g_pdl ? 1 : 0;
+  attr[1].id = cudaLaunchAttributeClusterDimension;
+  attr[1].val.clusterDim.x = (unsigned)split;
+  attr[1].val.clusterDim.y = 1;
+  attr[1].val.clusterDim.z = 1;
+  cfg->attrs = attr;
+  cfg->numAttrs = 2;
+}
+
+// How many clusters of `split` CTAs are resident at once with 2 CTAs per SM. Clusters of 8 have to fit inside one
+// GPC: measured on B200, a 224-CTA grid of 8-clusters runs in one wave while 288 CTAs do not (scripts/
+// profile_linear.py splits), hence ~30 of them. (cudaOccupancyMaxActiveClusters answers 148 / 74 / 33 / 15 here,
+// i.e. for one CTA per SM, which is not what the launches do.)
+template <typename T, int kMode>
+int resident_clusters(int split) {
+  const int sms = sm_count();
+  return split == 8 ? 30 * sms / 148 : 2 * sms / split;
+}
+
+// split-K factor (cluster size 1, 2, 4 or 8). Streaming model: a CTA keeps 4 K-blocks (64 KB of weights) in flight,
+// i.e. ~2.5 blocks/us at loaded HBM latency; the device moves ~390 blocks/us (6.4 TB/s); the reduce-scatter costs
+// a few hundred ns per doubling. Pick the smallest split that reaches the best modelled time.
+template <typename T, int kMode>
 int choose_split(int n_tiles, int k_blocks) {
-  if (g_force_split > 0) return g_force_split < k_blocks ? g_force_split : k_blocks;
-  const int slots = 2 * sm_count();
+  if (g_force_split > 0) return g_force_split;
   int best = 1;
-  double best_cost = 1e30;
-  for (int s = 1; s <= k_blocks && s <= 32; ++s) {
-    const int waves = (n_tiles * s + slots - 1) / slots;
-    const double cost = waves * ((k_blocks + s - 1) / s + 4.0) + 0.25 * s;
-    if (cost < best_cost - 1e-9) {
-      best_cost = cost;
+  double best_t = 1e30;
+  const double device_rate = 390.0 * sm_count() / 148.0;
+  for (int s = 1; s <= 8 && s <= k_blocks; s *= 2) {
+    const int cap = resident_clusters<T, kMode>(s);
+    const double conc = (double)(n_tiles < cap ? n_tiles : cap) * s;
+    const double rate = conc * 2.5 < device_rate ? conc * 2.5 : device_rate;
+    const double t = (double)n_tiles * k_blocks / rate + (s > 1 ? 1.0 + 0.4 * s : 0.0);
+    if (t < best_t * 0.97) {
+      best_t = t;
       best = s;
     }
   }
   return best;
 }
 
-constexpr size_t kCounterBytes = kMaxTiles * sizeof(int);
-
 template <typename T, int kMode>
-int launch_t(const CUtensorMap& tw, const CUtensorMap& tx, const Params& p, int n_tiles, cudaStream_t stream) {
+int launch_t(const CUtensorMap& tw, const CUtensorMap& tx, Params p, int n_tiles, cudaStream_t stream) {
   auto kern = linear_decode_sm100_kernel<T, kMode>;
   static bool attr_set = false;  // per template instantiation
   if (!attr_set) {
     CRAM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemRequest));
     attr_set = true;
   }
+  p.split = choose_split<T, kMode>(n_tiles, p.k_blocks);
+  static int launches = 0;
+  p.trace_slot = launches++;
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3((unsigned)(n_tiles * p.split));
-  cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = kSmemRequest;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // see griddep_wait in the kernel
-  attr[0].val.programmaticStreamSerializationAllowed = g_pdl ? 1 : 0;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cudaLaunchAttribute attr[2];
+  fill_config(&cfg, attr, n_tiles * p.split, p.split, stream);
   CRAM_CUDA(cudaLaunchKernelEx(&cfg, kern, tw, tx, p));
   return check_launch("linear_decode_sm100_kernel");
 }
@@ -335,19 +461,24 @@ int launch_t(const CUtensorMap& tw, const CUtensorMap& tx, const Params& p, int 
 
 using namespace cram;
 
+#ifdef CRAM_LINEAR_TRACE
+extern "C" int cram_debug_linear_trace(unsigned long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, cram::g_lin_trace, sizeof(cram::g_lin_trace)) == cudaSuccess ? 0 : -1;
+}
+#endif
 extern "C" void cram_debug_linear_split(int split) { g_force_split = split; }
+// resident clusters of 1 / 2 / 4 / 8 CTAs for the bf16 mode-1 kernel, and the split chosen for (n_out, k, mode)
+extern "C" void cram_debug_linear_caps(int* caps4, int n_out, int k, int mode, int* split_out) {
+  int i = 0;
+  for (int s = 1; s <= 8; s *= 2) caps4[i++] = resident_clusters<__nv_bfloat16, 1>(s);
+  const int n_tiles = tiles_of(n_out, mode), kb = (k + kBlockK - 1) / kBlockK;
+  *split_out = mode == 0 ? choose_split<__nv_bfloat16, 0>(n_tiles, kb)
+                         : mode == 1 ? choose_split<__nv_bfloat16, 1>(n_tiles, kb) : choose_split<__nv_bfloat16, 2>(n_tiles, kb);
+}
 extern "C" void cram_debug_linear_pdl(int on) { g_pdl = on; }
 
-extern "C" size_t cram_linear_decode_workspace_bytes(int n_out, int k, int mode) {
-  if (n_out <= 0 || k <= 0) return 0;
-  const int n_tiles = tiles_of(n_out, mode);
-  const int split = choose_split(n_tiles, (k + kBlockK - 1) / kBlockK);
-  return kCounterBytes + (split > 1 ? (size_t)n_tiles * split * kTileN * kRows * sizeof(float) : 0);
-}
-
 extern "C" int cram_linear_decode(const void* x, int64_t ldx, int m, const void* w, int64_t ldw, int n_out, int k,
-                                  const void* bias, void* y, int64_t ldy, int mode, int dtype, void* workspace,
-                                  size_t workspace_bytes, cram_stream_t stream) {
+                                  const void* bias, void* y, int64_t ldy, int mode, int dtype, cram_stream_t stream) {
   CRAM_REQUIRE(dtype == CRAM_BF16 || dtype == CRAM_F16, "cram_linear_decode: dtype must be bf16 or fp16");
   CRAM_REQUIRE(mode >= 0 && mode <= 2, "cram_linear_decode: mode must be 0 (bias), 1 (residual add) or 2 (SwiGLU)");
   CRAM_REQUIRE(m >= 0 && m <= kRows, "cram_linear_decode: at most %d rows (got %d)", kRows, m);
@@ -356,9 +487,7 @@ extern "C" int cram_linear_decode(const void* x, int64_t ldx, int m, const void*
   CRAM_REQUIRE(k % 8 == 0 && ldx % 8 == 0 && ldw % 8 == 0, "cram_linear_decode: k and the x / w row strides must be multiples of 8");
   auto mis = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) != 0; };
   CRAM_REQUIRE(!mis(x) && !mis(w), "cram_linear_decode: x and w must be 16-byte aligned");
-  CRAM_REQUIRE(workspace && !mis(workspace), "cram_linear_decode: workspace missing");
   const int n_tiles = tiles_of(n_out, mode);
-  CRAM_REQUIRE(n_tiles <= kMaxTiles, "cram_linear_decode: n_out too large");
   Params p{};
   p.y = y;
   p.ldy = ldy;
@@ -366,12 +495,8 @@ extern "C" int cram_linear_decode(const void* x, int64_t ldx, int m, const void*
   p.m = m;
   p.n_out = n_out;
   p.k_blocks = (k + kBlockK - 1) / kBlockK;
-  p.split = choose_split(n_tiles, p.k_blocks);
+  p.split = 1;
   p.up_row0 = n_out;
-  const size_t need = kCounterBytes + (p.split > 1 ? (size_t)n_tiles * p.split * kTileN * kRows * sizeof(float) : 0);
-  CRAM_REQUIRE(workspace_bytes >= need, "cram_linear_decode: workspace of %zu bytes, need %zu", workspace_bytes, need);
-  p.counters = reinterpret_cast<int*>(workspace);  // zero before the first use; every launch leaves them zero
-  p.partials = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kCounterBytes);
   CUtensorMap tw, tx;
   int rc;
   if ((rc = tmap_rows_by_k(&tw, w, dtype, mode == 2 ? 2 * (int64_t)n_out : n_out, k, ldw)) != CRAM_OK) return rc;

@@ -11,6 +11,7 @@ Rows of all sequences are packed ([sum(T_i), hidden]); ``cu_seqlens`` delimits t
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence
 
@@ -79,6 +80,8 @@ class CramEngine:
             raise ops.CramError("CramEngine needs CUDA weights: cram_b200 has no CPU fallback")
         self._rope_len = 0
         self._ensure_rope(max_positions)
+        # decode steps of <= 64 sequences run the MLP through cram_linear_decode (CRAM_B200_STREAMING_MLP=0: library GEMMs)
+        self.streaming_mlp = os.environ.get("CRAM_B200_STREAMING_MLP", "1") != "0"
 
     # ---- construction -------------------------------------------------------------------------------
     @staticmethod
@@ -169,11 +172,17 @@ class CramEngine:
         a, b = s.num_heads * s.head_dim, (s.num_heads + s.num_kv_heads) * s.head_dim
         return qkv[:, :a], qkv[:, a:b], qkv[:, b:]
 
-    def layer_post(self, l: int, x: torch.Tensor, attn: torch.Tensor) -> torch.Tensor:
-        """o_proj + residual + MLP of layer l. x is updated in place; returns the pending MLP delta."""
+    def layer_post(self, l: int, x: torch.Tensor, attn: torch.Tensor, streaming_mlp: bool = False) -> Optional[torch.Tensor]:
+        """o_proj + residual + MLP of layer l. x is updated in place; returns the pending MLP delta, or None when
+        the delta is already in x (``streaming_mlp``: the <= 64-row decode step, where gate/up + SwiGLU and
+        down + residual add each run as one weight-streaming launch of cram_linear_decode)."""
         s = self.spec
         o = F.linear(attn, self.w[f"wo.{l}"])
         h = ops.rmsnorm(x, self.w[f"post_norm.{l}"], s.rms_eps, residual=o)
+        if streaming_mlp:
+            act = ops.linear_decode(h, self.w[f"wgu.{l}"], mode=ops.LINEAR_SWIGLU)
+            ops.linear_decode(act, self.w[f"wdown.{l}"], mode=ops.LINEAR_RESIDUAL, out=x)
+            return None
         act = ops.silu_mul(F.linear(h, self.w[f"wgu.{l}"]))
         return F.linear(act, self.w[f"wdown.{l}"])
 
@@ -240,14 +249,16 @@ class CramEngine:
         slot = block_table.gather(1, (pos64 // ps)[:, None]).squeeze(1).to(torch.int64) * ps + pos64 % ps
         x = F.embedding(tokens, self.w["embed"])
         pending = None
+        streaming = self.streaming_mlp and x.shape[0] <= 64 and x.dtype in (torch.bfloat16, torch.float16)
         for l in range(s.num_layers):
             qkv = self._qkv(l, x, pending, positions, kv, slot)
             q, k, v = self.split_qkv(qkv)
             mask = int(head_masks[l]) if (head_masks is not None and logcred is not None) else 0
             attn = ops.attn_decode(q, kv.k[l], kv.v[l], block_table, seqlens, max_seqlen, s.num_heads, s.num_kv_heads,
                                    s.head_dim, logcred=logcred, head_mask=mask, bias_len=bias_len, workspace=workspace)
-            pending = self.layer_post(l, x, attn)
-        x.add_(pending)
+            pending = self.layer_post(l, x, attn, streaming_mlp=streaming)
+        if pending is not None:
+            x.add_(pending)
         return self.logits(x)
 
     @torch.no_grad()

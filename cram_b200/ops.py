@@ -216,21 +216,9 @@ def rope_kv_append_(qkv: torch.Tensor, n_heads: int, n_kv_heads: int, head_dim: 
 
 
 LINEAR_PLAIN, LINEAR_RESIDUAL, LINEAR_SWIGLU = 0, 1, 2
-_linear_ws: dict = {}
-
-
-def linear_decode_workspace(n_out: int, k: int, mode: int, device) -> torch.Tensor:
-    """One zero-initialised workspace per device, grown to the largest request (launches are stream-ordered)."""
-    need = int(_lib.load().cram_linear_decode_workspace_bytes(n_out, k, mode))
-    ws = _linear_ws.get(str(device))
-    if ws is None or ws.numel() < need:
-        ws = torch.zeros(max(need, 1 << 24), dtype=torch.uint8, device=device)
-        _linear_ws[str(device)] = ws
-    return ws
-
 
 def linear_decode(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, mode: int = LINEAR_PLAIN,
-                  out: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
+                  out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Decode-step projection of <= 64 rows (cram_linear_decode). mode LINEAR_PLAIN: x @ w.T (+ bias);
     LINEAR_RESIDUAL: out += x @ w.T in place (out is the residual stream); LINEAR_SWIGLU: w = [gate; up] rows,
     returns silu(x @ gate.T) * (x @ up.T)."""
@@ -245,11 +233,8 @@ def linear_decode(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor]
         assert mode != LINEAR_RESIDUAL, "LINEAR_RESIDUAL adds into `out`"
         out = torch.empty((m, n_out), dtype=x.dtype, device=x.device)
     assert out.shape == (m, n_out) and out.stride(1) == 1 and out.dtype == x.dtype
-    if workspace is None:
-        workspace = linear_decode_workspace(n_out, k, mode, x.device)
     check(lib.cram_linear_decode(_ptr(x), x.stride(0), m, _ptr(w), w.stride(0), n_out, k, _ptr(bias), _ptr(out),
-                                 out.stride(0), mode, dtype_code(x.dtype), _ptr(workspace), workspace.numel(), _stream()),
-          "cram_linear_decode")
+                                 out.stride(0), mode, dtype_code(x.dtype), _stream()), "cram_linear_decode")
     launch_count += 1
     return out
 

@@ -191,12 +191,10 @@ int cram_rope_kv_append(void* qkv, int64_t row_stride, int64_t n_rows, int n_hea
  *   mode 1: y[m, n] += T(sum_k x[m,k] w[n,k])                 the residual add of o_proj / down_proj, in place
  *   mode 2: y[m, n] = T(T(silu(T(g))) * T(u)), g = x . w[n], u = x . w[n_out + n]     w = [2 n_out, k] (gate, up):
  *           LlamaMLP act_fn(gate_proj(x)) * up_proj(x) (transformers modeling_llama.py LlamaMLP.forward)
- * bf16 / fp16; k and the row strides multiples of 8; workspace from cram_linear_decode_workspace_bytes, its first
- * 16 KB zeroed once by the caller (ticket counters; every launch leaves them zero). */
-size_t cram_linear_decode_workspace_bytes(int n_out, int k, int mode);
+ * bf16 / fp16; k and the row strides multiples of 8. Split-K runs inside a thread-block cluster (reduction in
+ * distributed shared memory): no workspace, results independent of timing. */
 int cram_linear_decode(const void* x, int64_t ldx, int m, const void* w, int64_t ldw, int n_out, int k,
-                       const void* bias, void* y, int64_t ldy, int mode, int dtype, void* workspace,
-                       size_t workspace_bytes, cram_stream_t stream);
+                       const void* bias, void* y, int64_t ldy, int mode, int dtype, cram_stream_t stream);
 /* out[r, j] = silu(gate_up[r, j]) * gate_up[r, inter + j] */
 int cram_silu_mul(const void* gate_up, void* out, int64_t n_rows, int inter, int dtype, cram_stream_t stream);
 

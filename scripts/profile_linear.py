@@ -74,12 +74,44 @@ if len(sys.argv) > 2 and sys.argv[2] == "eager":  # for ncu: a few plain launche
             ops.linear_decode(x, w, None, mode=mode, out=y)
     torch.cuda.synchronize()
     sys.exit(0)
+if len(sys.argv) > 2 and sys.argv[2] == "chain":
+    # the MLP half of a decode layer as the engine runs it: rmsnorm -> gate/up (+SwiGLU) -> down (+residual)
+    from cram_b200 import _lib
+    import ctypes
+    lib = _lib.load()
+    lib.cram_debug_linear_pdl.argtypes = [ctypes.c_int]
+    wgu = [(torch.randn(2 * I, H, device=dev) * 0.02).to(torch.bfloat16) for _ in range(L)]
+    wd = [(torch.randn(H, I, device=dev) * 0.02).to(torch.bfloat16) for _ in range(L)]
+    nw = torch.ones(H, device=dev, dtype=torch.bfloat16)
+    x = torch.randn(64, H, device=dev).to(torch.bfloat16)
+
+    def chain(gu_ours, down_ours):
+        def fn():
+            pending = None
+            for l in range(L):
+                h = ops.rmsnorm(x, nw, 1e-6, residual=pending)
+                act = ops.linear_decode(h, wgu[l], mode=2) if gu_ours else ops.silu_mul(F.linear(h, wgu[l]))
+                if down_ours:
+                    ops.linear_decode(act, wd[l], mode=1, out=x)
+                    pending = None
+                else:
+                    pending = F.linear(act, wd[l])
+        return fn
+
+    for pdl in (0, 1):
+        lib.cram_debug_linear_pdl(pdl)
+        for gu_ours in (False, True):
+            for down_ours in (False, True):
+                x.normal_()
+                print(f"pdl {pdl}  gate/up {'ours' if gu_ours else 'lib '}  down {'ours' if down_ours else 'lib '}: "
+                      f"{graph_time(chain(gu_ours, down_ours)):7.2f} us per layer (MLP half)", flush=True)
+    sys.exit(0)
 if len(sys.argv) > 2 and sys.argv[2] == "splits":
     from cram_b200 import _lib
     import ctypes
     lib = _lib.load()
     lib.cram_debug_linear_split.argtypes = [ctypes.c_int]
-    for sp in (1, 2, 4, 8, 10, 16):
+    for sp in (1, 2, 4, 8):
         lib.cram_debug_linear_split(sp)
         print("forced split", sp, flush=True)
         case("qkv  4608x3584 +bias", QKV, H, 0, True)

@@ -182,3 +182,33 @@ def test_run_rag_batch_equals_reference_loop_at_b1(engine32):
     # and the public single-sample call is that same path (utils/re_weighting.py:115-138)
     one = rw.run_RAG_with_attention_weighting(question=qs[0], paras=ps[0], scores=ss[0])
     assert one[0] == batched[0][0] and one[1].startswith(batched[0][1])
+
+
+def test_streaming_mlp_decode_step_matches_the_library_gemm_path():
+    """bf16 decode step with the MLP on cram_linear_decode (SwiGLU and residual-add epilogues) vs the same step on
+    library GEMMs + glue kernels: same roundings, different fp32 accumulation order -> logits agree to bf16 noise
+    and the greedy continuation is the same wherever the top-2 margin exceeds that noise."""
+    from cram_b200.engine import PagedKV
+    spec = ModelSpec(3, 8, 2, 64, 512, 1408, 500, 1e-6, 10000.0, qkv_bias=True)
+    eng = CramEngine.random_init(spec, seed=3, dtype=torch.bfloat16, device=DEV, std=0.05)
+    B, ps, ctx = 5, 16, 70
+    n_pages = B * 8
+    g = torch.Generator(device=DEV).manual_seed(1)
+    out = {}
+    for streaming in (False, True):
+        eng.streaming_mlp = streaming
+        kv = PagedKV(spec, n_pages, ps, torch.bfloat16, DEV)
+        for l in range(spec.num_layers):
+            kv.k[l].copy_(torch.randn(kv.k[l].shape, device=DEV, generator=torch.Generator(device=DEV).manual_seed(10 + l)))
+            kv.v[l].copy_(torch.randn(kv.v[l].shape, device=DEV, generator=torch.Generator(device=DEV).manual_seed(20 + l)))
+        bt = torch.arange(n_pages, device=DEV, dtype=torch.int32).view(B, 8)
+        tokens = torch.tensor([5, 17, 250, 499, 42], device=DEV)
+        positions = torch.full((B,), ctx, device=DEV, dtype=torch.int32)
+        out[streaming] = eng.decode_step(tokens, positions, kv, bt, positions + 1, ctx + 1).float()
+    a, b = out[False], out[True]
+    assert torch.isfinite(b).all()
+    scale = a.abs().max().item()
+    assert (a - b).abs().max().item() <= 0.03 * scale + 1e-3
+    top2 = a.topk(2, dim=-1).values
+    sure = (top2[:, 0] - top2[:, 1]) > 0.06 * scale
+    assert bool((a.argmax(-1) == b.argmax(-1))[sure].all())
