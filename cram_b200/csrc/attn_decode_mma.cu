@@ -90,6 +90,9 @@ attn_decode_mma_kernel(const cram_attn_decode_params p, const int n_splits, floa
   extern __shared__ __align__(128) uint8_t dsm[];
   const uint32_t smem0 = (uint32_t)__cvta_generic_to_shared(dsm);
 
+  // programmatic dependent launch (common.cuh): resident early, but nothing is read before the predecessor is done
+  pdl_launch_dependents();
+  pdl_wait();
   const int split = blockIdx.x, kvh = blockIdx.y, seq = blockIdx.z;
   const int n_rep = p.n_heads / p.n_kv_heads;
   const int h_base = kvh * n_rep;
@@ -359,7 +362,7 @@ int launch_mma_t(const cram_attn_decode_params& p, int n_splits, cudaStream_t st
     attr_set[pow2] = true;
   }
   dim3 grid(n_splits, p.n_kv_heads, p.n_seq);
-  kern<<<grid, kMmaThreads, smem, stream>>>(p, n_splits, reinterpret_cast<float*>(p.workspace));
+  CRAM_CUDA(launch_pdl(true, kern, grid, dim3(kMmaThreads), smem, stream, p, n_splits, reinterpret_cast<float*>(p.workspace)));
   return check_launch("attn_decode_mma_kernel");
 }
 

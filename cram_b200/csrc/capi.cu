@@ -17,6 +17,8 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+int g_pdl = 1;
+
 int sm_count() {
   static int n = 0;
   if (n == 0) {
@@ -85,3 +87,5 @@ extern "C" int cram_rank_heads(const double* scores, int n_samples, int n_layers
   }
   return CRAM_OK;
 }
+
+extern "C" void cram_debug_pdl(int on) { cram::g_pdl = on; }

@@ -43,6 +43,31 @@ inline int check_launch(const char* what) {
 // B200: 148 SMs. Queried once per process; used to size persistent grids.
 int sm_count();
 
+// Programmatic dependent launch for the decode step's chain of short kernels: a kernel launched this way may become
+// resident while its predecessor in the stream is still running; it must execute pdl_wait() before touching
+// anything the predecessor wrote, and calls pdl_launch_dependents() so that ITS successor can do the same. Both are
+// no-ops for a normally launched kernel. `early` is set for decode-sized launches only (a prefill-sized grid gains
+// nothing from it). cram_debug_pdl(0) switches the attribute off (A/B timing).
+extern int g_pdl;
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(bool early, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = (g_pdl && early) ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 template <typename T>
 struct DType;
 template <>

@@ -34,6 +34,8 @@ rmsnorm_kernel(T* __restrict__ x, const T* __restrict__ residual, const T* __res
   constexpr int N = Vec<T>::N;
   __shared__ float s_part[kNormThreads / 32];
   __shared__ float s_inv;
+  pdl_launch_dependents();
+  pdl_wait();
   T* xr = x + (int64_t)blockIdx.x * hidden;
   const T* rr = residual ? residual + (int64_t)blockIdx.x * hidden : nullptr;
   T* orow = out + (int64_t)blockIdx.x * hidden;
@@ -243,6 +245,8 @@ __global__ void rope_kv_append_kernel(T* __restrict__ qkv, int64_t row_stride, i
   const int half = head_dim / 2;
   const int vec_per_head = half / N;
   const int heads_all = n_heads + 2 * n_kv_heads;
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t per_row = (int64_t)heads_all * vec_per_head;
   const int64_t total = n_rows * per_row;
   for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
@@ -316,8 +320,8 @@ extern "C" int cram_rmsnorm(void* x, const void* residual, const void* weight, v
   CRAM_REQUIRE(aligned16(x) && aligned16(weight) && aligned16(out) && (!residual || aligned16(residual)),
                "cram_rmsnorm: pointers must be 16-byte aligned");
   CRAM_REQUIRE(n_rows < (1ll << 31), "cram_rmsnorm: too many rows");
-  DISPATCH_DTYPE(dtype, (rmsnorm_kernel<T><<<(unsigned)n_rows, kNormThreads, 0, (cudaStream_t)stream>>>(
-                            (T*)x, (const T*)residual, (const T*)weight, (T*)out, hidden, eps)));
+  DISPATCH_DTYPE(dtype, (launch_pdl(n_rows <= 256, rmsnorm_kernel<T>, dim3((unsigned)n_rows), dim3(kNormThreads), 0, (cudaStream_t)stream,
+                                    (T*)x, (const T*)residual, (const T*)weight, (T*)out, hidden, eps)));
   return check_launch("rmsnorm_kernel");
 }
 
@@ -348,10 +352,10 @@ extern "C" int cram_rope_kv_append(void* qkv, int64_t row_stride, int64_t n_rows
   CRAM_REQUIRE(aligned16(qkv) && aligned16(cos_table) && aligned16(sin_table) && aligned16(k_cache) && aligned16(v_cache),
                "cram_rope_kv_append: pointers must be 16-byte aligned");
   const int64_t items = n_rows * (n_heads + 2 * n_kv_heads) * (head_dim / 2 / vec);
-  DISPATCH_DTYPE(dtype, (rope_kv_append_kernel<T><<<stream_grid(items, 256), 256, 0, (cudaStream_t)stream>>>(
-                            (T*)qkv, row_stride, n_rows, n_heads, n_kv_heads, head_dim, (const T*)cos_table,
-                            (const T*)sin_table, positions, slot_mapping, (T*)k_cache, (T*)v_cache, page_stride,
-                            token_stride, page_size)));
+  DISPATCH_DTYPE(dtype, (launch_pdl(n_rows <= 256, rope_kv_append_kernel<T>, dim3(stream_grid(items, 256)), dim3(256), 0, (cudaStream_t)stream,
+                                    (T*)qkv, row_stride, n_rows, n_heads, n_kv_heads, head_dim, (const T*)cos_table,
+                                    (const T*)sin_table, positions, slot_mapping, (T*)k_cache, (T*)v_cache, page_stride,
+                                    token_stride, page_size)));
   return check_launch("rope_kv_append_kernel");
 }
 

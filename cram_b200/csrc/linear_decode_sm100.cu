@@ -387,7 +387,6 @@ int tmap_rows_by_k(CUtensorMap* m, const void* base, int dtype, int64_t rows, in
 
 inline int tiles_of(int n_out, int mode) { return mode == 2 ? (n_out + 63) / 64 : (n_out + kTileN - 1) / kTileN; }
 
-int g_pdl = 1;          // programmatic dependent launch (cram_debug_linear_pdl switches it off for A/B timing)
 int g_force_split = 0;  // scripts/profile_linear.py only (cram_debug_linear_split)
 
 void fill_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid, int split, cudaStream_t stream) {
@@ -475,7 +474,7 @@ extern "C" void cram_debug_linear_caps(int* caps4, int n_out, int k, int mode, i
   *split_out = mode == 0 ? choose_split<__nv_bfloat16, 0>(n_tiles, kb)
                          : mode == 1 ? choose_split<__nv_bfloat16, 1>(n_tiles, kb) : choose_split<__nv_bfloat16, 2>(n_tiles, kb);
 }
-extern "C" void cram_debug_linear_pdl(int on) { g_pdl = on; }
+extern "C" void cram_debug_linear_pdl(int on) { g_pdl = on; }  // same switch as cram_debug_pdl
 
 extern "C" int cram_linear_decode(const void* x, int64_t ldx, int m, const void* w, int64_t ldw, int n_out, int k,
                                   const void* bias, void* y, int64_t ldy, int mode, int dtype, cram_stream_t stream) {
