@@ -82,6 +82,8 @@ class CramEngine:
         self._ensure_rope(max_positions)
         # decode steps of <= 64 sequences run the MLP through cram_linear_decode (CRAM_B200_STREAMING_MLP=0: library GEMMs)
         self.streaming_mlp = os.environ.get("CRAM_B200_STREAMING_MLP", "1") != "0"
+        # the two small projections (qkv, o_proj) as well; off by default: the library GEMM is faster at 25-33 MB
+        self.streaming_proj = os.environ.get("CRAM_B200_STREAMING_PROJ", "0") != "0"
 
     # ---- construction -------------------------------------------------------------------------------
     @staticmethod
@@ -159,7 +161,10 @@ class CramEngine:
         rows also go to their cache slots in the same launch as the rotation."""
         s = self.spec
         h = ops.rmsnorm(x, self.w[f"in_norm.{l}"], s.rms_eps, residual=pending)  # x += pending (in place)
-        qkv = F.linear(h, self.w[f"wqkv.{l}"], self.w.get(f"bqkv.{l}"))
+        if self.streaming_proj and kv is not None and h.shape[0] <= 64 and h.dtype in (torch.bfloat16, torch.float16):
+            qkv = ops.linear_decode(h, self.w[f"wqkv.{l}"], self.w.get(f"bqkv.{l}"))
+        else:
+            qkv = F.linear(h, self.w[f"wqkv.{l}"], self.w.get(f"bqkv.{l}"))
         if kv is None:
             ops.rope_(qkv, s.num_heads + s.num_kv_heads, s.head_dim, self.cos, self.sin, positions)
         else:
@@ -177,8 +182,12 @@ class CramEngine:
         the delta is already in x (``streaming_mlp``: the <= 64-row decode step, where gate/up + SwiGLU and
         down + residual add each run as one weight-streaming launch of cram_linear_decode)."""
         s = self.spec
-        o = F.linear(attn, self.w[f"wo.{l}"])
-        h = ops.rmsnorm(x, self.w[f"post_norm.{l}"], s.rms_eps, residual=o)
+        if streaming_mlp and self.streaming_proj:
+            ops.linear_decode(attn, self.w[f"wo.{l}"], mode=ops.LINEAR_RESIDUAL, out=x)
+            h = ops.rmsnorm(x, self.w[f"post_norm.{l}"], s.rms_eps)
+        else:
+            o = F.linear(attn, self.w[f"wo.{l}"])
+            h = ops.rmsnorm(x, self.w[f"post_norm.{l}"], s.rms_eps, residual=o)
         if streaming_mlp:
             act = ops.linear_decode(h, self.w[f"wgu.{l}"], mode=ops.LINEAR_SWIGLU)
             ops.linear_decode(act, self.w[f"wdown.{l}"], mode=ops.LINEAR_RESIDUAL, out=x)
