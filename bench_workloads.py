@@ -225,7 +225,37 @@ def run_decode(args):
         ms_attn_graph = timed_steps(D, g_attn.replay, reps)
         dec_avg_ms = ms_attn_graph / spec.num_layers
 
+        # ---- the decode MLP kernel (cram_linear_decode), timed the same way: every layer's gate/up + SwiGLU and
+        # down + residual launches on the engine's own weights, in one graph
+        mlp = None
+        if engine.streaming_mlp and B <= 64:
+            h_s = torch.randn(B, spec.hidden, device=dev).bfloat16()
+            x_s = torch.zeros(B, spec.hidden, device=dev, dtype=torch.bfloat16)
+            act_s = torch.empty(B, spec.intermediate, device=dev, dtype=torch.bfloat16)
+
+            def mlp_only():
+                for l in range(spec.num_layers):
+                    ops.linear_decode(h_s, engine.w[f"wgu.{l}"], mode=ops.LINEAR_SWIGLU, out=act_s)
+                    ops.linear_decode(act_s, engine.w[f"wdown.{l}"], mode=ops.LINEAR_RESIDUAL, out=x_s)
+
+            mlp_only()
+            torch.cuda.synchronize()
+            g_mlp = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g_mlp):
+                mlp_only()
+            g_mlp.replay()
+            ms_mlp = timed_steps(D, g_mlp.replay, reps) / spec.num_layers
+            mlp_bytes = 3.0 * spec.hidden * spec.intermediate * 2
+            mlp = {"kernel": "linear_decode_sm100_kernel<bf16> (gate/up + SwiGLU, down + residual add)",
+                   "ms_per_layer": ms_mlp, "weight_bytes_per_layer": mlp_bytes, "achieved": mlp_bytes / (ms_mlp / 1e3) / 1e9,
+                   "unit": "GB/s", "launches_timed": reps * spec.num_layers * 2,
+                   "timing": "CUDA events around replays of a graph holding the step's two MLP launches of every layer"}
+
     peak, peak_sus, hbm, which = measured_peaks()
+    if mlp is not None:
+        mlp["peak"] = hbm
+        mlp["frac"] = mlp["achieved"] / hbm
+        mlp["share_of_step"] = mlp["ms_per_layer"] * spec.num_layers / (ms_step / new)
     kv_bytes = float(sum(n + new // 2 for n in lens)) * 2 * spec.num_kv_heads * spec.head_dim * 2
     achieved = kv_bytes / (dec_avg_ms / 1e3) / 1e9
     p_layer = spec.hidden * (spec.num_heads + 2 * spec.num_kv_heads) * spec.head_dim + spec.num_heads * spec.head_dim * spec.hidden \
@@ -242,6 +272,7 @@ def run_decode(args):
                 "bytes_per_launch": kv_bytes,
                 "timing": "CUDA events around replays of a graph holding the step's attention launches (all layers, real caches)",
                 "attn_share_of_step": dec_avg_ms * spec.num_layers / ms_token_step,
+                "decode_mlp": mlp,
                 "model_level": {"achieved": model_gbs, "peak": hbm, "frac": model_gbs / hbm, "ms_per_token_step": ms_token_step,
                                 "note": "weights once + KV once per token step / graph-replayed step time"}}
     cpu_baseline = None

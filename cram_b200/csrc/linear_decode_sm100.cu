@@ -466,15 +466,6 @@ extern "C" int cram_debug_linear_trace(unsigned long long* host_out) {
 }
 #endif
 extern "C" void cram_debug_linear_split(int split) { g_force_split = split; }
-// resident clusters of 1 / 2 / 4 / 8 CTAs for the bf16 mode-1 kernel, and the split chosen for (n_out, k, mode)
-extern "C" void cram_debug_linear_caps(int* caps4, int n_out, int k, int mode, int* split_out) {
-  int i = 0;
-  for (int s = 1; s <= 8; s *= 2) caps4[i++] = resident_clusters<__nv_bfloat16, 1>(s);
-  const int n_tiles = tiles_of(n_out, mode), kb = (k + kBlockK - 1) / kBlockK;
-  *split_out = mode == 0 ? choose_split<__nv_bfloat16, 0>(n_tiles, kb)
-                         : mode == 1 ? choose_split<__nv_bfloat16, 1>(n_tiles, kb) : choose_split<__nv_bfloat16, 2>(n_tiles, kb);
-}
-extern "C" void cram_debug_linear_pdl(int on) { g_pdl = on; }  // same switch as cram_debug_pdl
 
 extern "C" int cram_linear_decode(const void* x, int64_t ldx, int m, const void* w, int64_t ldw, int n_out, int k,
                                   const void* bias, void* y, int64_t ldy, int mode, int dtype, cram_stream_t stream) {
