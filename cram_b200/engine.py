@@ -258,7 +258,8 @@ class CramEngine:
         slot = block_table.gather(1, (pos64 // ps)[:, None]).squeeze(1).to(torch.int64) * ps + pos64 % ps
         x = F.embedding(tokens, self.w["embed"])
         pending = None
-        streaming = self.streaming_mlp and x.shape[0] <= 64 and x.dtype in (torch.bfloat16, torch.float16)
+        streaming = (self.streaming_mlp and x.shape[0] <= 64 and x.dtype in (torch.bfloat16, torch.float16)
+                     and s.hidden % 8 == 0 and s.intermediate % 8 == 0)  # what cram_linear_decode takes
         for l in range(s.num_layers):
             qkv = self._qkv(l, x, pending, positions, kv, slot)
             q, k, v = self.split_qkv(qkv)
