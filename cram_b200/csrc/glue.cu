@@ -81,23 +81,24 @@ rmsnorm_kernel(T* __restrict__ x, const T* __restrict__ residual, const T* __res
 // Rotary embedding in place on the first n_rot_heads heads of each row (Q heads then K heads of a
 // fused QKV buffer). out = x*cos + rotate_half(x)*sin with HF's three roundings.
 // ------------------------------------------------------------------------------------------------
-template <typename T>
+// I: index type of the flattened (row, head, vector) space -- int32 whenever it fits (a 64-bit division per item
+// costs more than the item's arithmetic)
+template <typename T, typename I>
 __global__ void rope_kernel(T* __restrict__ qk, int64_t row_stride, int64_t n_rows, int n_rot_heads, int head_dim,
                             const T* __restrict__ cos_t, const T* __restrict__ sin_t,
                             const int32_t* __restrict__ positions) {
   constexpr int N = Vec<T>::N;
   const int half = head_dim / 2;
   const int vec_per_head = half / N;
-  const int64_t per_row = (int64_t)n_rot_heads * vec_per_head;
-  const int64_t total = n_rows * per_row;
-  for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
-       idx += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = idx / per_row;
+  const I per_row = (I)n_rot_heads * vec_per_head;
+  const I total = (I)n_rows * per_row;
+  for (I idx = blockIdx.x * (I)blockDim.x + threadIdx.x; idx < total; idx += (I)gridDim.x * blockDim.x) {
+    const I r = idx / per_row;
     const int rem = (int)(idx - r * per_row);
     const int h = rem / vec_per_head;
     const int j = (rem - h * vec_per_head) * N;
     const int pos = positions[r];
-    T* base = qk + r * row_stride + (int64_t)h * head_dim;
+    T* base = qk + (int64_t)r * row_stride + (int64_t)h * head_dim;
     Vec<T> x1 = ldvec(base + j), x2 = ldvec(base + j + half);
     Vec<T> c1 = ldvec(cos_t + (int64_t)pos * head_dim + j), c2 = ldvec(cos_t + (int64_t)pos * head_dim + j + half);
     Vec<T> s1 = ldvec(sin_t + (int64_t)pos * head_dim + j), s2 = ldvec(sin_t + (int64_t)pos * head_dim + j + half);
@@ -131,6 +132,8 @@ __global__ void silu_mul_kernel(const T* __restrict__ gu, T* __restrict__ out, i
     Vec<T> g = ldvec(gu + r * 2 * inter + j), u = ldvec(gu + r * 2 * inter + inter + j), o;
 #pragma unroll
     for (int e = 0; e < N; ++e) {
+      // exact expf + IEEE divide: 599 us at [32852 x 2 x 14336] against 427 us for the bare stream; deciding the rounding
+      // from ex2.approx / rcp.approx with an exact fallback near ties was bit-identical but slower (637-733 us: branches)
       const float x = DType<T>::to_f(g.v[e]);
       const float s = round_to<T>(x / (1.0f + expf(-x)));
       o.v[e] = DType<T>::from_f(s * DType<T>::to_f(u.v[e]));
@@ -235,7 +238,7 @@ __global__ void kv_append_kernel(const uint4* __restrict__ k, const uint4* __res
 // two). Work item = (row, head, 16-byte vector j of the first half of the head): Q heads are rotated in place, K heads
 // are rotated in place AND written to the cache slot, V heads are copied to the cache slot. Same arithmetic as
 // rope_kernel (products rounded to T before the add, as torch does).
-template <typename T>
+template <typename T, typename I>
 __global__ void rope_kv_append_kernel(T* __restrict__ qkv, int64_t row_stride, int64_t n_rows, int n_heads, int n_kv_heads,
                                       int head_dim, const T* __restrict__ cos_t, const T* __restrict__ sin_t,
                                       const int32_t* __restrict__ positions, const int64_t* __restrict__ slot_mapping,
@@ -247,15 +250,14 @@ __global__ void rope_kv_append_kernel(T* __restrict__ qkv, int64_t row_stride, i
   const int heads_all = n_heads + 2 * n_kv_heads;
   pdl_launch_dependents();
   pdl_wait();
-  const int64_t per_row = (int64_t)heads_all * vec_per_head;
-  const int64_t total = n_rows * per_row;
-  for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
-       idx += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = idx / per_row;
+  const I per_row = (I)heads_all * vec_per_head;
+  const I total = (I)n_rows * per_row;
+  for (I idx = blockIdx.x * (I)blockDim.x + threadIdx.x; idx < total; idx += (I)gridDim.x * blockDim.x) {
+    const I r = idx / per_row;
     const int rem = (int)(idx - r * per_row);
     const int h = rem / vec_per_head;
     const int j = (rem - h * vec_per_head) * N;
-    T* base = qkv + r * row_stride + (int64_t)h * head_dim;
+    T* base = qkv + (int64_t)r * row_stride + (int64_t)h * head_dim;
     Vec<T> x1 = ldvec(base + j), x2 = ldvec(base + j + half);
     const int64_t slot = slot_mapping[r];
     if (h >= n_heads + n_kv_heads) {  // V head: copy only
@@ -334,9 +336,15 @@ extern "C" int cram_rope(void* qk, int64_t row_stride, int64_t n_rows, int n_rot
   CRAM_REQUIRE((head_dim / 2) % vec == 0 && row_stride % vec == 0, "cram_rope: head_dim/2 and row_stride must be multiples of %d", vec);
   CRAM_REQUIRE(aligned16(qk) && aligned16(cos_table) && aligned16(sin_table), "cram_rope: pointers must be 16-byte aligned");
   const int64_t items = n_rows * n_rot_heads * (head_dim / 2 / vec);
-  DISPATCH_DTYPE(dtype, (rope_kernel<T><<<stream_grid(items, 256), 256, 0, (cudaStream_t)stream>>>(
-                            (T*)qk, row_stride, n_rows, n_rot_heads, head_dim, (const T*)cos_table,
-                            (const T*)sin_table, positions)));
+  if (items + (int64_t)sm_count() * 16 * 256 < (1ll << 31)) {
+    DISPATCH_DTYPE(dtype, (rope_kernel<T, int><<<stream_grid(items, 256), 256, 0, (cudaStream_t)stream>>>(
+                              (T*)qk, row_stride, n_rows, n_rot_heads, head_dim, (const T*)cos_table,
+                              (const T*)sin_table, positions)));
+  } else {
+    DISPATCH_DTYPE(dtype, (rope_kernel<T, int64_t><<<stream_grid(items, 256), 256, 0, (cudaStream_t)stream>>>(
+                              (T*)qk, row_stride, n_rows, n_rot_heads, head_dim, (const T*)cos_table,
+                              (const T*)sin_table, positions)));
+  }
   return check_launch("rope_kernel");
 }
 
@@ -352,10 +360,17 @@ extern "C" int cram_rope_kv_append(void* qkv, int64_t row_stride, int64_t n_rows
   CRAM_REQUIRE(aligned16(qkv) && aligned16(cos_table) && aligned16(sin_table) && aligned16(k_cache) && aligned16(v_cache),
                "cram_rope_kv_append: pointers must be 16-byte aligned");
   const int64_t items = n_rows * (n_heads + 2 * n_kv_heads) * (head_dim / 2 / vec);
-  DISPATCH_DTYPE(dtype, (launch_pdl(n_rows <= 256, rope_kv_append_kernel<T>, dim3(stream_grid(items, 256)), dim3(256), 0, (cudaStream_t)stream,
-                                    (T*)qkv, row_stride, n_rows, n_heads, n_kv_heads, head_dim, (const T*)cos_table,
-                                    (const T*)sin_table, positions, slot_mapping, (T*)k_cache, (T*)v_cache, page_stride,
-                                    token_stride, page_size)));
+  if (items + (int64_t)sm_count() * 16 * 256 < (1ll << 31)) {
+    DISPATCH_DTYPE(dtype, (launch_pdl(n_rows <= 256, rope_kv_append_kernel<T, int>, dim3(stream_grid(items, 256)), dim3(256), 0,
+                                      (cudaStream_t)stream, (T*)qkv, row_stride, n_rows, n_heads, n_kv_heads, head_dim,
+                                      (const T*)cos_table, (const T*)sin_table, positions, slot_mapping, (T*)k_cache,
+                                      (T*)v_cache, page_stride, token_stride, page_size)));
+  } else {
+    DISPATCH_DTYPE(dtype, (launch_pdl(false, rope_kv_append_kernel<T, int64_t>, dim3(stream_grid(items, 256)), dim3(256), 0,
+                                      (cudaStream_t)stream, (T*)qkv, row_stride, n_rows, n_heads, n_kv_heads, head_dim,
+                                      (const T*)cos_table, (const T*)sin_table, positions, slot_mapping, (T*)k_cache,
+                                      (T*)v_cache, page_stride, token_stride, page_size)));
+  }
   return check_launch("rope_kv_append_kernel");
 }
 

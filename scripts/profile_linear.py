@@ -79,7 +79,7 @@ if len(sys.argv) > 2 and sys.argv[2] == "chain":
     from cram_b200 import _lib
     import ctypes
     lib = _lib.load()
-    lib.cram_debug_linear_pdl.argtypes = [ctypes.c_int]
+    lib.cram_debug_pdl.argtypes = [ctypes.c_int]
     wgu = [(torch.randn(2 * I, H, device=dev) * 0.02).to(torch.bfloat16) for _ in range(L)]
     wd = [(torch.randn(H, I, device=dev) * 0.02).to(torch.bfloat16) for _ in range(L)]
     nw = torch.ones(H, device=dev, dtype=torch.bfloat16)
@@ -99,7 +99,7 @@ if len(sys.argv) > 2 and sys.argv[2] == "chain":
         return fn
 
     for pdl in (0, 1):
-        lib.cram_debug_linear_pdl(pdl)
+        lib.cram_debug_pdl(pdl)
         for gu_ours in (False, True):
             for down_ours in (False, True):
                 x.normal_()
@@ -120,9 +120,9 @@ if len(sys.argv) > 2 and sys.argv[2] == "splits":
 from cram_b200 import _lib as _l
 import ctypes as _c
 _lb = _l.load()
-_lb.cram_debug_linear_pdl.argtypes = [_c.c_int]
+_lb.cram_debug_pdl.argtypes = [_c.c_int]
 for pdl in (0, 1):
-    _lb.cram_debug_linear_pdl(pdl)
+    _lb.cram_debug_pdl(pdl)
     print("programmatic dependent launch", pdl, flush=True)
     case("qkv  4608x3584 +bias", QKV, H, 0, True)
     case("o    3584x3584 +residual", H, H, 1)

@@ -27,9 +27,9 @@ def run(which, split, pdl):
     from cram_b200 import ops, _lib
     lib = _lib.load()
     lib.cram_debug_linear_split.argtypes = [ctypes.c_int]
-    lib.cram_debug_linear_pdl.argtypes = [ctypes.c_int]
+    lib.cram_debug_pdl.argtypes = [ctypes.c_int]
     lib.cram_debug_linear_split(split)
-    lib.cram_debug_linear_pdl(pdl)
+    lib.cram_debug_pdl(pdl)
     H, I, QKV = 3584, 18944, 4608
     n_rows_w, k, mode = {"qkv": (QKV, H, 0), "o": (H, H, 1), "gu": (2 * I, H, 2), "down": (H, I, 1)}[which]
     dev = "cuda"

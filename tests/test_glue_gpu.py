@@ -84,6 +84,26 @@ def test_silu_mul(dtype):
         assert (got.float() - want.float()).abs().max().item() <= 0.07
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_silu_mul_all_gate_bit_patterns(dtype):
+    """Every one of the 65 536 gate values of the dtype (the kernel decides the rounding of silu from a fast
+    estimate and falls back to the exact expression near ties): bit-equal to T(T(g / (1 + expf(-g))) * u)
+    evaluated in fp32 by torch on the same device, for several u."""
+    bits = torch.arange(65536, dtype=torch.int32, device=DEV).to(torch.int16)
+    g = bits.view(dtype)
+    finite = torch.isfinite(g.float())
+    gf = g.float()
+    s = (gf / (1.0 + torch.exp(-gf))).to(dtype)  # the expression of cram_silu_mul / HF eager, rounded once
+    for uval in (1.0, -0.7421875, 3.0, 0.001953125):
+        u = torch.full_like(g, uval)
+        gu = torch.cat([g.view(64, 1024), u.view(64, 1024)], dim=1).contiguous()
+        got = ops.silu_mul(gu).reshape(-1)
+        want = (s.float() * u.float()).to(dtype)
+        same = (got.view(torch.int16) == want.view(torch.int16)) | ((got == 0) & (want == 0))
+        bad = finite & ~same & ~(torch.isnan(got.float()) & torch.isnan(want.float()))
+        assert int(bad.sum()) == 0, (uval, g[bad][:8], got[bad][:8], want[bad][:8])
+
+
 def test_splice_and_answer_ie():
     torch.manual_seed(3)
     T, H, dh, hidden, V, n = 50, 4, 64, 256, 1000, 3
