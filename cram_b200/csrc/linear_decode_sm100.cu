@@ -31,7 +31,8 @@ namespace {
 constexpr int kTileN = 128;   // weight rows per tile (UMMA M, TMEM lanes)
 constexpr int kRows = 64;     // token rows (UMMA N, TMEM columns)
 constexpr int kBlockK = 64;   // one 128-byte swizzle slab of bf16/fp16
-constexpr int kRing = 4;
+constexpr int kRingShared = 4;  // two CTAs per SM: grids that fill the machine
+constexpr int kRingDeep = 8;    // one CTA per SM: small projections (<= #SM CTAs), twice the weights in flight per CTA
 constexpr int kWBytes = kTileN * kBlockK * 2;  // 16 KB
 constexpr int kXBytes = kRows * kBlockK * 2;   // 8 KB
 constexpr int kStageBytes = kWBytes + kXBytes;
@@ -39,13 +40,17 @@ constexpr int kThreads = 192;  // warps 0-3 epilogue, warp 4 producer, warp 5 MM
 constexpr int kTmemCols = 64;
 constexpr uint32_t kDescHi = ptx::umma_desc_hi(1024);
 
+template <int kRing>
 struct Bars {
   uint64_t full[kRing], empty[kRing];
   uint64_t acc_full;
   uint32_t tmem_ptr;
 };
-constexpr int kSmemRequest = kRing * kStageBytes + (int)sizeof(Bars) + 1024;
-static_assert(kTileN * kRows * 4 <= kRing * kStageBytes, "the reduce-scatter buffer reuses the drained ring");
+template <int kRing>
+constexpr int smem_request() {
+  return kRing * kStageBytes + (int)sizeof(Bars<kRing>) + 1024;
+}
+static_assert(kTileN * kRows * 4 <= kRingShared * kStageBytes, "the reduce-scatter buffer reuses the drained ring");
 
 // Debug timeline (scripts/profile_linear.py trace builds a separate library with -DCRAM_LINEAR_TRACE; the product
 // build compiles none of this): %globaltimer stamps of every CTA of the last 32 launches.
@@ -188,13 +193,13 @@ __device__ __forceinline__ void cluster_reduce_and_store(const Params& p, const 
   store_rows<T, kMode, kMS>(p, n, (int)rank * kMS, v, kMode == 2 ? up : v, pre);
 }
 
-template <typename T, int kMode>
-__global__ void __launch_bounds__(kThreads, 2)
+template <typename T, int kMode, int kRing>
+__global__ void __launch_bounds__(kThreads, kRing == kRingShared ? 2 : 1)
 linear_decode_sm100_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                            const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  Bars* bar = reinterpret_cast<Bars*>(smem + kRing * kStageBytes);
+  Bars<kRing>* bar = reinterpret_cast<Bars<kRing>*>(smem + kRing * kStageBytes);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // grid = tiles x split, the `split` CTAs of a tile are consecutive (= one cluster)
   const int tile = blockIdx.x / p.split, sp = blockIdx.x - tile * p.split;
@@ -389,10 +394,12 @@ inline int tiles_of(int n_out, int mode) { return mode == 2 ? (n_out + 63) / 64 
 
 int g_force_split = 0;  // scripts/profile_linear.py only (cram_debug_linear_split)
 
-void fill_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid, int split, cudaStream_t stream) {
+int g_force_ring = 0;   // 0 = by grid size, 4 / 8 = forced (scripts/profile_linear.py only)
+
+void fill_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid, int split, int smem, cudaStream_t stream) {
   cfg->gridDim = dim3((unsigned)grid);
   cfg->blockDim = dim3(kThreads);
-  cfg->dynamicSmemBytes = kSmemRequest;
+  cfg->dynamicSmemBytes = smem;
   cfg->stream = stream;
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // see griddep_wait in the kernel
   attr[0].val.programmaticStreamSerializationAllowed = g_pdl ? 1 : 0;
@@ -408,25 +415,31 @@ void fill_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int grid, i
 // GPC: measured on B200, a 224-CTA grid of 8-clusters runs in one wave while 288 CTAs do not (scripts/
 // profile_linear.py splits), hence ~30 of them. (cudaOccupancyMaxActiveClusters answers 148 / 74 / 33 / 15 here,
 // i.e. for one CTA per SM, which is not what the launches do.)
-template <typename T, int kMode>
 int resident_clusters(int split) {
   const int sms = sm_count();
   return split == 8 ? 30 * sms / 148 : 2 * sms / split;
 }
 
-// split-K factor (cluster size 1, 2, 4 or 8). Streaming model: a CTA keeps 4 K-blocks (64 KB of weights) in flight,
-// i.e. ~2.5 blocks/us at loaded HBM latency; the device moves ~390 blocks/us (6.4 TB/s); the reduce-scatter costs
-// a few hundred ns per doubling. Pick the smallest split that reaches the best modelled time.
-template <typename T, int kMode>
+// A grid of at most #SM CTAs runs one CTA per SM and takes the 8-stage ring (128 KB of weights in flight per CTA:
+// under programmatic dependent launch most of a small projection is on chip before its input exists).
+bool deep_ring(int n_tiles, int split) {
+  if (g_force_ring) return g_force_ring == kRingDeep;
+  return n_tiles * split <= sm_count();
+}
+
+// split-K factor (cluster size 1, 2, 4 or 8). Streaming model: a CTA keeps its ring (4 or 8 K-blocks of 16 KB of
+// weights) in flight, i.e. ~2.5 or ~5 blocks/us at loaded HBM latency; the device moves ~390 blocks/us (6.4 TB/s);
+// the reduce-scatter costs a few hundred ns per doubling. Pick the smallest split that reaches the best modelled time.
 int choose_split(int n_tiles, int k_blocks) {
   if (g_force_split > 0) return g_force_split;
   int best = 1;
   double best_t = 1e30;
   const double device_rate = 390.0 * sm_count() / 148.0;
   for (int s = 1; s <= 8 && s <= k_blocks; s *= 2) {
-    const int cap = resident_clusters<T, kMode>(s);
+    const int cap = resident_clusters(s);
     const double conc = (double)(n_tiles < cap ? n_tiles : cap) * s;
-    const double rate = conc * 2.5 < device_rate ? conc * 2.5 : device_rate;
+    const double per_cta = deep_ring(n_tiles, s) ? 5.0 : 2.5;
+    const double rate = conc * per_cta < device_rate ? conc * per_cta : device_rate;
     const double t = (double)n_tiles * k_blocks / rate + (s > 1 ? 1.0 + 0.4 * s : 0.0);
     if (t < best_t * 0.97) {
       best_t = t;
@@ -436,22 +449,28 @@ int choose_split(int n_tiles, int k_blocks) {
   return best;
 }
 
-template <typename T, int kMode>
-int launch_t(const CUtensorMap& tw, const CUtensorMap& tx, Params p, int n_tiles, cudaStream_t stream) {
-  auto kern = linear_decode_sm100_kernel<T, kMode>;
+template <typename T, int kMode, int kRing>
+int launch_r(const CUtensorMap& tw, const CUtensorMap& tx, const Params& p, int n_tiles, cudaStream_t stream) {
+  auto kern = linear_decode_sm100_kernel<T, kMode, kRing>;
   static bool attr_set = false;  // per template instantiation
   if (!attr_set) {
-    CRAM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemRequest));
+    CRAM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_request<kRing>()));
     attr_set = true;
   }
-  p.split = choose_split<T, kMode>(n_tiles, p.k_blocks);
-  static int launches = 0;
-  p.trace_slot = launches++;
   cudaLaunchConfig_t cfg{};
   cudaLaunchAttribute attr[2];
-  fill_config(&cfg, attr, n_tiles * p.split, p.split, stream);
+  fill_config(&cfg, attr, n_tiles * p.split, p.split, smem_request<kRing>(), stream);
   CRAM_CUDA(cudaLaunchKernelEx(&cfg, kern, tw, tx, p));
   return check_launch("linear_decode_sm100_kernel");
+}
+
+template <typename T, int kMode>
+int launch_t(const CUtensorMap& tw, const CUtensorMap& tx, Params p, int n_tiles, cudaStream_t stream) {
+  p.split = choose_split(n_tiles, p.k_blocks);
+  static int launches = 0;
+  p.trace_slot = launches++;
+  return deep_ring(n_tiles, p.split) ? launch_r<T, kMode, kRingDeep>(tw, tx, p, n_tiles, stream)
+                                     : launch_r<T, kMode, kRingShared>(tw, tx, p, n_tiles, stream);
 }
 
 }  // namespace
@@ -466,6 +485,7 @@ extern "C" int cram_debug_linear_trace(unsigned long long* host_out) {
 }
 #endif
 extern "C" void cram_debug_linear_split(int split) { g_force_split = split; }
+extern "C" void cram_debug_linear_ring(int ring) { g_force_ring = ring; }
 
 extern "C" int cram_linear_decode(const void* x, int64_t ldx, int m, const void* w, int64_t ldw, int n_out, int k,
                                   const void* bias, void* y, int64_t ldy, int mode, int dtype, cram_stream_t stream) {

@@ -111,10 +111,13 @@ if len(sys.argv) > 2 and sys.argv[2] == "splits":
     import ctypes
     lib = _lib.load()
     lib.cram_debug_linear_split.argtypes = [ctypes.c_int]
-    for sp in (1, 2, 4, 8):
+    lib.cram_debug_linear_ring.argtypes = [ctypes.c_int]
+    for sp, ring in ((2, 8), (4, 4), (4, 8), (8, 4)):
         lib.cram_debug_linear_split(sp)
-        print("forced split", sp, flush=True)
+        lib.cram_debug_linear_ring(ring)
+        print("forced split", sp, "ring", ring, flush=True)
         case("qkv  4608x3584 +bias", QKV, H, 0, True)
+        case("o    3584x3584 +residual", H, H, 1)
         case("down 3584x18944 +residual", H, I, 1)
     sys.exit(0)
 from cram_b200 import _lib as _l
