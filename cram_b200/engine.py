@@ -84,6 +84,11 @@ class CramEngine:
         self.streaming_mlp = os.environ.get("CRAM_B200_STREAMING_MLP", "1") != "0"
         # the two small projections (qkv, o_proj) as well; off by default: the library GEMM is faster at 25-33 MB
         self.streaming_proj = os.environ.get("CRAM_B200_STREAMING_PROJ", "0") != "0"
+        if os.environ.get("CRAM_B200_PDL"):  # A/B timing only: 0 switches programmatic dependent launch off
+            import ctypes
+            lib = ops._lib.load()
+            lib.cram_debug_pdl.argtypes = [ctypes.c_int]
+            lib.cram_debug_pdl(int(os.environ["CRAM_B200_PDL"]))
         if os.environ.get("CRAM_B200_LINEAR_RING"):  # A/B timing only: force the 4- or 8-stage ring everywhere
             import ctypes
             lib = ops._lib.load()
