@@ -389,15 +389,19 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       if (n_max > 0) load_k_and_bias(0);
       if (n_max > 1) load_k_and_bias(1);
       for (int j = 0; j < n_max; ++j) {
+        if (lane == 0) CRAM_TRACE(10, j, 0);
         if (j + 2 < n_max) load_k_and_bias(j + 2);
         const int st = j % kKV;
         if (lane == 0) {
+          CRAM_TRACE(10, j, 1);
           ptx::mbar_wait(&bar->v_empty[st], ((j / kKV) & 1) ^ 1);
+          CRAM_TRACE(10, j, 2);
           ptx::mbar_expect_tx(&bar->v_full[st], S::kTileBytes);
 #pragma unroll
           for (int sl = 0; sl < kSlabs; ++sl)
             ptx::tma_load_2d(smem + S::kV + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_v, &bar->v_full[st],
                              kv_head * DH + sl * 64, k0 + j * kBlockN);
+          CRAM_TRACE(10, j, 3);
         }
         __syncwarp();
       }
