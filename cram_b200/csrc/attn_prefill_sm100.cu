@@ -154,8 +154,15 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
   uint32_t s[2][32];
   const uint64_t sc2 = pk2(scale2, scale2);
   float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-  // TMEM -> registers in two 32-column chunks; the load of chunk c+1 is in flight while chunk c gets
-  // its bias FFMA2 and running max.
+  // Speculative exponentials: the reference max only moves when a tile beats it by more than 2^8 (lazy rescale), so
+  // almost every tile ends up using the m_ref it started with. The exps are therefore issued against that value in
+  // the SAME pass that forms the scores and the tile max -- the MUFU pipe runs under the FFMA2 / max stream instead
+  // of after it -- and are redone only if some row of the warp does move its reference (first tiles, rare later).
+  const float m_spec = (m_ref == -INFINITY) ? 0.f : m_ref;
+  const uint64_t negm_spec = pk2(-m_spec, -m_spec);
+  uint64_t la = pk2(0.f, 0.f), lb = pk2(0.f, 0.f);
+  uint32_t pk[32];
+  // TMEM -> registers in two 32-column chunks; the load of chunk c+1 is in flight while chunk c is processed.
   ptx::tmem_ld32(s_addr, s[0]);
 #pragma unroll
   for (int c = 0; c < 2; ++c) {
@@ -165,8 +172,8 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
     for (int i = 0; i < 32; i += 4) {
       uint64_t bx, by;
       asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(bx), "=l"(by) : "r"(bias + (c * 32 + i) * 4));
-      const uint64_t t01 = ffma2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), sc2, bx);
-      const uint64_t t23 = ffma2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), sc2, by);
+      uint64_t t01 = ffma2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), sc2, bx);
+      uint64_t t23 = ffma2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), sc2, by);
       float t0, t1, t2, t3;
       upk2(t01, t0, t1);
       upk2(t23, t2, t3);
@@ -176,6 +183,8 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
         t1 = (col + 1 <= climit) ? t1 : -INFINITY;
         t2 = (col + 2 <= climit) ? t2 : -INFINITY;
         t3 = (col + 3 <= climit) ? t3 : -INFINITY;
+        t01 = pk2(t0, t1);
+        t23 = pk2(t2, t3);
       }
       s[c][i + 0] = __float_as_uint(t0);
       s[c][i + 1] = __float_as_uint(t1);
@@ -188,6 +197,16 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
         mx0 = fmax3(mx0, t0, t1);
         mx1 = fmax3(mx1, t2, t3);
       }
+#ifndef CRAM_NO_SPEC_SOFTMAX
+      float e0, e1, e2, e3;
+      upk2(fadd2(t01, negm_spec), e0, e1);
+      upk2(fadd2(t23, negm_spec), e2, e3);
+      const float p0 = ex2(e0), p1 = ex2(e1), p2 = ex2(e2), p3 = ex2(e3);
+      la = fadd2(la, pk2(p0, p1));
+      lb = fadd2(lb, pk2(p2, p3));
+      pk[c * 16 + i / 2 + 0] = pack2<T>(p0, p1);
+      pk[c * 16 + i / 2 + 1] = pack2<T>(p2, p3);
+#endif
     }
   }
   const float mxa = fmaxf(mx0, mx1), mxb = fmaxf(mx2, mx3);
@@ -196,45 +215,51 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
   // lazy rescale: move the reference max only when this tile beats it by more than 2^8
   const bool need = mx > m_ref + kRescaleThreshold;
   const float m_new = need ? mx : m_ref;
-  if (!first && __any_sync(0xffffffffu, need)) {
-    const float f = need ? ex2(m_ref - m_new) : 1.0f;  // m_ref = -inf gives 0
-    ptx::mbar_wait(o_done_bar, o_done_parity);         // P V of the previous tile has landed in O
-    ptx::tc_fence_after();
-    const uint64_t f2 = pk2(f, f);
+#ifndef CRAM_NO_SPEC_SOFTMAX
+  const bool redo = __any_sync(0xffffffffu, need);
+#else
+  const bool redo = true;
+#endif
+  if (redo) {
+    if (!first && __any_sync(0xffffffffu, need)) {
+      const float f = need ? ex2(m_ref - m_new) : 1.0f;  // m_ref = -inf gives 0
+      ptx::mbar_wait(o_done_bar, o_done_parity);         // P V of the previous tile has landed in O
+      ptx::tc_fence_after();
+      const uint64_t f2 = pk2(f, f);
 #pragma unroll
-    for (int c = 0; c < DH / 32; ++c) {
-      uint32_t o[32];
-      ptx::tmem_ld32(o_addr + c * 32, o);
-      ptx::tc_wait_ld();
+      for (int c = 0; c < DH / 32; ++c) {
+        uint32_t o[32];
+        ptx::tmem_ld32(o_addr + c * 32, o);
+        ptx::tc_wait_ld();
 #pragma unroll
-      for (int i = 0; i < 32; i += 2) {
-        float a, b;
-        upk2(fmul2(pk2(__uint_as_float(o[i]), __uint_as_float(o[i + 1])), f2), a, b);
-        o[i] = __float_as_uint(a);
-        o[i + 1] = __float_as_uint(b);
+        for (int i = 0; i < 32; i += 2) {
+          float a, b;
+          upk2(fmul2(pk2(__uint_as_float(o[i]), __uint_as_float(o[i + 1])), f2), a, b);
+          o[i] = __float_as_uint(a);
+          o[i + 1] = __float_as_uint(b);
+        }
+        ptx::tmem_st32(o_addr + c * 32, o);
       }
-      ptx::tmem_st32(o_addr + c * 32, o);
+      l *= f;
     }
-    l *= f;
-  }
-  m_ref = m_new;
-  const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
-  const uint64_t negm = pk2(-m_use, -m_use);
-
-  uint64_t la = pk2(0.f, 0.f), lb = pk2(0.f, 0.f);
-  uint32_t pk[32];
+    m_ref = m_new;
+    const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
+    const uint64_t negm = pk2(-m_use, -m_use);
+    la = pk2(0.f, 0.f);
+    lb = pk2(0.f, 0.f);
 #pragma unroll
-  for (int c = 0; c < 2; ++c) {
+    for (int c = 0; c < 2; ++c) {
 #pragma unroll
-    for (int i = 0; i < 32; i += 4) {
-      float e0, e1, e2, e3;
-      upk2(fadd2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), negm), e0, e1);
-      upk2(fadd2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), negm), e2, e3);
-      const float p0 = ex2(e0), p1 = ex2(e1), p2 = ex2(e2), p3 = ex2(e3);
-      la = fadd2(la, pk2(p0, p1));
-      lb = fadd2(lb, pk2(p2, p3));
-      pk[c * 16 + i / 2 + 0] = pack2<T>(p0, p1);
-      pk[c * 16 + i / 2 + 1] = pack2<T>(p2, p3);
+      for (int i = 0; i < 32; i += 4) {
+        float e0, e1, e2, e3;
+        upk2(fadd2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), negm), e0, e1);
+        upk2(fadd2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), negm), e2, e3);
+        const float p0 = ex2(e0), p1 = ex2(e1), p2 = ex2(e2), p3 = ex2(e3);
+        la = fadd2(la, pk2(p0, p1));
+        lb = fadd2(lb, pk2(p2, p3));
+        pk[c * 16 + i / 2 + 0] = pack2<T>(p0, p1);
+        pk[c * 16 + i / 2 + 1] = pack2<T>(p2, p3);
+      }
     }
   }
   ptx::tmem_st32(s_addr, pk);  // P over the S columns: 64 keys -> 32 packed columns
