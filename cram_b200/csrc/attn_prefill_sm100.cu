@@ -380,11 +380,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     setmaxnreg_dec<56>();
     if (warp == 8) {
       // ============================== producer ==================================================
-      // Order K[0], K[1], then per step t: K[t+2] (+ its bias vector), V[t] -- Q K^T runs two tiles
-      // ahead of P V. The bias vector of tile j lives until every P V[j] is done; the ring of 8 is
-      // safe because slot j&7 is rewritten only after the V slot of tile j-6 was seen free.
-      const bool biased = p.logcred != nullptr && ((p.head_mask >> head) & 1ull);
-      const int bias_len = p.bias_len ? p.bias_len[seq] : len_k;
+      // Order K[0], K[1], then per step t: K[t+2], V[t] -- Q K^T runs two tiles ahead of P V.
       auto load_k_and_bias = [&](int j) {
         const int st = j % kKV;
         if (lane == 0 && j >= 2) {  // K[0], K[1] were issued before the CTA-wide sync
@@ -395,21 +391,6 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             ptx::tma_load_2d(smem + S::kK + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_k, &bar->k_full[st],
                              kv_head * DH + sl * 64, k0 + j * kBlockN);
         }
-        {
-          float2 b2;
-          float* bp = reinterpret_cast<float*>(&b2);
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const int key = j * kBlockN + lane * 2 + e;
-            float v = 0.f;
-            if (key >= len_k) v = -INFINITY;
-            else if (biased && key < bias_len) v = load_logcred(p.logcred, (int64_t)k0 + key, p.logcred_dtype) * kLog2e;
-            bp[e] = v;
-          }
-          reinterpret_cast<float2*>(s_bias + (j % kBiasRing) * kBlockN)[lane] = b2;
-        }
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&bar->bias_full[j % kBiasRing]);
       };
       if (n_max > 0) load_k_and_bias(0);
       if (n_max > 1) load_k_and_bias(1);
@@ -429,6 +410,31 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
           CRAM_TRACE(10, j, 3);
         }
         __syncwarp();
+      }
+    } else if (warp == 10) {
+      // ============================== bias vectors ===============================================
+      // Its own warp (on a different sub-partition than the TMA producer): the log-credibility loads are dependent
+      // global loads, and behind the TMA issue they kept the producer one tile ahead instead of four. The vector of
+      // tile j (already x log2e, -inf past the key length) lives in a ring of 8 until every P V[j] is done; tile j is
+      // written once the V slot of tile j-4 has been seen free (the producer's own condition for V[j], so the phase
+      // parity cannot alias: that barrier's next completion needs this very vector) -- four tiles of slack.
+      const bool biased = p.logcred != nullptr && ((p.head_mask >> head) & 1ull);
+      const int bias_len = p.bias_len ? p.bias_len[seq] : len_k;
+      for (int j = 0; j < n_max; ++j) {
+        if (j >= kKV) ptx::mbar_wait(&bar->v_empty[j % kKV], ((j / kKV) & 1) ^ 1);
+        float2 b2;
+        float* bp = reinterpret_cast<float*>(&b2);
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int key = j * kBlockN + lane * 2 + e;
+          float v = 0.f;
+          if (key >= len_k) v = -INFINITY;
+          else if (biased && key < bias_len) v = load_logcred(p.logcred, (int64_t)k0 + key, p.logcred_dtype) * kLog2e;
+          bp[e] = v;
+        }
+        reinterpret_cast<float2*>(s_bias + (j % kBiasRing) * kBlockN)[lane] = b2;
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&bar->bias_full[j % kBiasRing]);
       }
     } else if (warp == 9 && ptx::elect_one_sync()) {
       // ============================== MMA issuer ================================================
