@@ -17,13 +17,15 @@
 // CTA = 256 query rows (two 128-row tiles, "stages" 0 and 1) of one (sequence, head); 12 warps:
 //   warps 0-3   softmax of stage 0 (TMEM lanes 32w..32w+31), correction and epilogue of that stage
 //   warps 4-7   same for stage 1
-//   warp  8     producer: TMA loads of Q0, Q1, K[j], V[j]; builds the per-tile bias vector
+//   warp  8     producer: TMA loads of Q0, Q1, K[j], V[j]
 //   warp  9     MMA issuer (one elected lane); owns the TMEM allocation
-//   warps 10-11 idle (they exist so that setmaxnreg can hand their registers to the softmax warps)
+//   warp  10    builds the per-tile bias vectors (log-credibility x log2e, -inf past the key length), 4 tiles ahead
+//   warp  11    idle (warps 8-11 exist so that setmaxnreg can hand their registers to the softmax warps)
 // The two stages share every K/V tile (half the shared-memory traffic per FLOP of a one-tile CTA) and
 // alternate on the tensor pipe: while warpgroup s runs the softmax of tile j, the MMA warp runs
 // P V (j) and Q K^T (j+1) of the other stage. TMEM: S0 | S1 | O0 | O1 (4 x 128 columns); P aliases S.
-// Lazy O rescale (only when a row's max grows by more than 2^8) keeps the correction off the hot loop.
+// Lazy O rescale (only when a row's max grows by more than 2^8) keeps the correction off the hot loop, and lets the
+// exponentials of a tile be issued speculatively against the standing reference max, in the pass that forms the scores.
 #include <mutex>
 #include <utility>
 
