@@ -351,7 +351,7 @@ def run_ours(args):
     step_flops = 2.0 * p_layer * spec.num_layers * total_tokens + attn_flops * spec.num_layers + 2.0 * spec.vocab * spec.hidden * args.batch
     model_tflops = step_flops / (ms_step / 1e3) / 1e12
     # the launches are timed with events INSIDE the long step (SM clock under the power cap): the sustained figure is
-    # the denominator; the burst one (the kernel alone does 797-814 TFLOP/s, scripts/profile_attn.py) is kept beside it
+    # the denominator; the burst one (the kernel alone does 842-853 TFLOP/s, scripts/profile_attn.py) is kept beside it
     roofline = {"bound": "tensor", "kernel": "attn_prefill_sm100_kernel<bf16,128>", "achieved": achieved, "peak": peak_sus,
                 "unit": "TFLOP/s", "frac": (achieved / peak_sus) if achieved else None,
                 "peak_burst": peak, "frac_of_burst": (achieved / peak) if achieved else None,
