@@ -184,6 +184,15 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; rank 0 alone works here, so give it the host's cores back
+    # (the count an un-launched `python bench.py --impl reference` gets: physical cores).
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        try:
+            import psutil
+            ncores = psutil.cpu_count(logical=False) or os.cpu_count()
+        except ImportError:
+            ncores = os.cpu_count()
+        torch.set_num_threads(max(1, min(ncores or 1, len(os.sched_getaffinity(0)))))
     nl = 2
     tps, ms, cores = cpu_reference_sample(args.seq, nl, max(1, args.steps), max(0, args.warmup))
     sample = (f"oracle port (reference is Python; /root/reference does not travel): {nl} of 32 layers x 1 of {args.batch} "
