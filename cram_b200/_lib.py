@@ -84,12 +84,25 @@ SIGNATURES = {
 }
 
 
+# A/B-timing switches exported by the library but deliberately NOT part of include/cram_b200.h (engine.py reads them
+# through the environment variables CRAM_B200_PDL / CRAM_B200_LINEAR_RING only).
+DEBUG_SIGNATURES = {
+    "cram_debug_pdl": (None, [C.c_int]),
+    "cram_debug_linear_ring": (None, [C.c_int]),
+}
+
+
 class CramError(RuntimeError):
     pass
 
 
 def library_path() -> str:
-    return _build.LIB_PATH
+    return os.environ.get("CRAM_B200_LIB") or _build.LIB_PATH
+
+
+def library_fingerprint() -> str:
+    """sha256 of csrc/ + the header + the nvcc flags the loaded in-tree library was built from (bench.py records it)."""
+    return _build.built_fingerprint()
 
 
 def load(build_if_missing: bool = True):
@@ -98,13 +111,23 @@ def load(build_if_missing: bool = True):
     with _lock:
         if _lib is not None:
             return _lib
-        path = os.environ.get("CRAM_B200_LIB") or _build.LIB_PATH  # override: debug builds (scripts/trace_attn.py)
-        if not os.path.exists(path):
-            if not build_if_missing:
+        path = os.environ.get("CRAM_B200_LIB")  # override: variant / debug builds (scripts/trace_attn.py)
+        if not path:
+            # The in-tree library must be the build of the sources next to it: a stale .so (sources edited, *.so is
+            # git-ignored but travels with the snapshot) would silently run old kernels. build_library() is a cheap
+            # fingerprint compare when nothing changed, a rebuild when nvcc is there, and an error otherwise.
+            path = _build.LIB_PATH
+            if os.path.exists(path) and not build_if_missing:
+                if not _build.is_current():
+                    raise CramError(f"{path} does not match cram_b200/csrc (stale build); run `python -m cram_b200.build`")
+            elif not os.path.exists(path) and not build_if_missing:
                 raise CramError(f"{path} is missing; run `python -m cram_b200.build` (no CPU fallback exists)")
-            path = _build.build_library()
+            else:
+                path = _build.build_library()
+        elif not os.path.exists(path):
+            raise CramError(f"CRAM_B200_LIB={path} does not exist")
         lib = C.CDLL(path)
-        for name, (res, args) in SIGNATURES.items():
+        for name, (res, args) in list(SIGNATURES.items()) + list(DEBUG_SIGNATURES.items()):
             fn = getattr(lib, name)  # AttributeError if the .so does not export a declared symbol
             fn.restype = res
             fn.argtypes = args

@@ -39,6 +39,15 @@ def _fingerprint() -> str:
     return h.hexdigest()
 
 
+def built_fingerprint() -> str:
+    stamp = os.path.join(BUILD_DIR, "fingerprint.txt")
+    return open(stamp).read().strip() if os.path.exists(stamp) else ""
+
+
+def is_current() -> bool:
+    return os.path.exists(LIB_PATH) and built_fingerprint() == _fingerprint()
+
+
 def build_library(force: bool = False, verbose: bool = False) -> str:
     """Compile every .cu for sm_100a and link the shared library. Returns its path."""
     os.makedirs(BUILD_DIR, exist_ok=True)

@@ -356,10 +356,10 @@ int launch_mma_t(const cram_attn_decode_params& p, int n_splits, cudaStream_t st
   constexpr size_t smem = ring > red ? ring : red;
   const bool pow2 = (p.page_size & (p.page_size - 1)) == 0;
   auto kern = pow2 ? attn_decode_mma_kernel<T, DH, true> : attn_decode_mma_kernel<T, DH, false>;
-  static bool attr_set[2] = {false, false};  // per template instantiation
-  if (!attr_set[pow2]) {
+  static PerDeviceOnce attr[2];  // per template instantiation, per device
+  if (!attr[pow2].flag()) {
     CRAM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set[pow2] = true;
+    attr[pow2].flag() = true;
   }
   dim3 grid(n_splits, p.n_kv_heads, p.n_seq);
   CRAM_CUDA(launch_pdl(true, kern, grid, dim3(kMmaThreads), smem, stream, p, n_splits, reinterpret_cast<float*>(p.workspace)));

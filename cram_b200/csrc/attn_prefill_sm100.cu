@@ -617,10 +617,10 @@ int launch_t(const cram_attn_prefill_params& p, cudaStream_t stream) {
   if (grid == 0) return CRAM_OK;
   CRAM_REQUIRE(grid < (1ll << 31), "cram_attn_prefill: grid too large");
   auto kern = attn_prefill_sm100_kernel<T, DH>;
-  static bool attr_set = false;  // per template instantiation
-  if (!attr_set) {
+  static PerDeviceOnce attr;  // per template instantiation, per device
+  if (!attr.flag()) {
     CRAM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<DH>::kRequest));
-    attr_set = true;
+    attr.flag() = true;
   }
   kern<<<(unsigned)grid, kThreads, Smem<DH>::kRequest, stream>>>(tq, tk, tv, p, num_pairs);
   return check_launch("attn_prefill_sm100_kernel");

@@ -20,16 +20,15 @@ void set_error(const char* fmt, ...) {
 int g_pdl = 1;
 
 int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0, v = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess &&
-        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
-      n = v;
-    else
-      n = 148;  // B200
+  static int n[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;  // B200
+  int& slot = n[dev & 63];
+  if (slot == 0) {
+    int v = 0;
+    slot = (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) ? v : 148;
   }
-  return n;
+  return slot;
 }
 
 }  // namespace cram

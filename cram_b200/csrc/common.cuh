@@ -40,8 +40,19 @@ inline int check_launch(const char* what) {
   return CRAM_OK;
 }
 
-// B200: 148 SMs. Queried once per process; used to size persistent grids.
+// B200: 148 SMs. Queried once per DEVICE (a process may drive several GPUs); used to size persistent grids.
 int sm_count();
+
+// One-time-per-device flag: cudaFuncSetAttribute is per device, so a `static bool` per template instantiation would
+// skip the attribute on the second GPU a process touches and the launch would fail there.
+struct PerDeviceOnce {
+  bool done[64] = {};
+  bool& flag() {
+    int d = 0;
+    cudaGetDevice(&d);
+    return done[d & 63];
+  }
+};
 
 // Programmatic dependent launch for the decode step's chain of short kernels: a kernel launched this way may become
 // resident while its predecessor in the stream is still running; it must execute pdl_wait() before touching

@@ -452,10 +452,10 @@ int choose_split(int n_tiles, int k_blocks) {
 template <typename T, int kMode, int kRing>
 int launch_r(const CUtensorMap& tw, const CUtensorMap& tx, const Params& p, int n_tiles, cudaStream_t stream) {
   auto kern = linear_decode_sm100_kernel<T, kMode, kRing>;
-  static bool attr_set = false;  // per template instantiation
-  if (!attr_set) {
+  static PerDeviceOnce smem_attr;  // per template instantiation, per device
+  if (!smem_attr.flag()) {
     CRAM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_request<kRing>()));
-    attr_set = true;
+    smem_attr.flag() = true;
   }
   cudaLaunchConfig_t cfg{};
   cudaLaunchAttribute attr[2];

@@ -85,15 +85,9 @@ class CramEngine:
         # the two small projections (qkv, o_proj) as well; off by default: the library GEMM is faster at 25-33 MB
         self.streaming_proj = os.environ.get("CRAM_B200_STREAMING_PROJ", "0") != "0"
         if os.environ.get("CRAM_B200_PDL"):  # A/B timing only: 0 switches programmatic dependent launch off
-            import ctypes
-            lib = ops._lib.load()
-            lib.cram_debug_pdl.argtypes = [ctypes.c_int]
-            lib.cram_debug_pdl(int(os.environ["CRAM_B200_PDL"]))
+            ops._lib.load().cram_debug_pdl(int(os.environ["CRAM_B200_PDL"]))
         if os.environ.get("CRAM_B200_LINEAR_RING"):  # A/B timing only: force the 4- or 8-stage ring everywhere
-            import ctypes
-            lib = ops._lib.load()
-            lib.cram_debug_linear_ring.argtypes = [ctypes.c_int]
-            lib.cram_debug_linear_ring(int(os.environ["CRAM_B200_LINEAR_RING"]))
+            ops._lib.load().cram_debug_linear_ring(int(os.environ["CRAM_B200_LINEAR_RING"]))
 
     # ---- construction -------------------------------------------------------------------------------
     @staticmethod
@@ -310,11 +304,14 @@ class CramEngine:
     def generate(self, prompts: Sequence[torch.Tensor], logcreds: Optional[Sequence[torch.Tensor]] = None,
                  head_masks: Optional[Sequence[int]] = None, max_new_tokens: int = 100,
                  eos_token_ids: Sequence[int] = (), bad_token_ids: Sequence[int] = (), page_size: int = 16,
-                 use_graph: bool = True, eos_check_every: int = 8) -> List[List[int]]:
+                 use_graph: bool = True, eos_check_every: int = 8, repetition_penalty: float = 1.0) -> List[List[int]]:
         """Greedy generation for a batch of prompts (each a 1-D int64 CUDA tensor) with per-sample
         credibility. Mirrors model.generate(do_sample=False, max_new_tokens=...) of
         utils/re_weighting.py:126-132: stop at EOS (the EOS token is kept), single-token bad words are
-        never emitted. Returns the new tokens of every sequence.
+        never emitted; ``repetition_penalty`` != 1 is what generate() still applies from the checkpoint's
+        generation_config under do_sample=False (RepetitionPenaltyLogitsProcessor: on the fp32 copy of the logits, every
+        token already in the sequence, prompt included, gets logit*p if negative else logit/p). Returns the new tokens of
+        every sequence.
 
         The decode step is captured once in a CUDA graph (DecodeSession) and replayed; generated tokens
         stay on the device and are read back every `eos_check_every` steps to test for EOS (tokens a
@@ -335,13 +332,19 @@ class CramEngine:
                 lc_dec[b, :lens[b]] = lc
             bias_len = torch.tensor(lens, dtype=torch.int32, device=dev)
         ban = torch.tensor(list(bad_token_ids), dtype=torch.int64, device=dev) if bad_token_ids else None
-        if ban is not None:
-            logits[:, ban] = float("-inf")
-        first = logits.argmax(-1)
-        sess = DecodeSession(self, kv, block_table, lens, max_new_tokens, logcred=lc_dec, bias_len=bias_len,
-                             head_masks=head_masks, bad_token_ids=bad_token_ids, use_graph=use_graph)
-        sess.start(first)
+        seen = None
+        if repetition_penalty != 1.0:
+            seen = torch.zeros(B, s.vocab, dtype=torch.bool, device=dev)
+            for b, p in enumerate(prompts):
+                seen[b, p.to(dev)] = True
+        first = greedy_pick(logits, ban, seen, repetition_penalty)
         eos = set(int(e) for e in eos_token_ids)
+        if max_new_tokens <= 1:  # nothing to decode: no session, no graph (its capture writes token row 1)
+            return [[int(t)] for t in first.tolist()] if max_new_tokens == 1 else [[] for _ in range(B)]
+        sess = DecodeSession(self, kv, block_table, lens, max_new_tokens, logcred=lc_dec, bias_len=bias_len,
+                             head_masks=head_masks, bad_token_ids=bad_token_ids, use_graph=use_graph, seen=seen,
+                             repetition_penalty=repetition_penalty)
+        sess.start(first)
         out: List[List[int]] = [[] for _ in range(B)]
         alive = [True] * B
         done_rows = 0
@@ -378,8 +381,10 @@ class DecodeSession:
 
     def __init__(self, engine: CramEngine, kv: PagedKV, block_table: torch.Tensor, prompt_lens: Sequence[int],
                  max_new_tokens: int, logcred: Optional[torch.Tensor] = None, bias_len: Optional[torch.Tensor] = None,
-                 head_masks: Optional[Sequence[int]] = None, bad_token_ids: Sequence[int] = (), use_graph: bool = True):
+                 head_masks: Optional[Sequence[int]] = None, bad_token_ids: Sequence[int] = (), use_graph: bool = True,
+                 seen: Optional[torch.Tensor] = None, repetition_penalty: float = 1.0):
         dev = engine.device
+        self.seen, self.repetition_penalty = seen, float(repetition_penalty)  # [B, vocab] bool: ids already in the sequence
         self.engine, self.kv, self.block_table = engine, kv, block_table
         self.logcred, self.bias_len, self.head_masks = logcred, bias_len, head_masks
         self.B = len(prompt_lens)
@@ -399,9 +404,9 @@ class DecodeSession:
         logits = self.engine.decode_step(self.tokens, self.positions, self.kv, self.block_table, self.seqlens,
                                          self.max_total, logcred=self.logcred, bias_len=self.bias_len,
                                          head_masks=self.head_masks)
-        if self.ban is not None:
-            logits[:, self.ban] = float("-inf")
-        nxt = logits.argmax(-1)
+        nxt = greedy_pick(logits, self.ban, self.seen, self.repetition_penalty)
+        if self.seen is not None:
+            self.seen.scatter_(1, nxt[:, None], True)
         self.out_tokens.index_copy_(0, self.step_idx, nxt[None])
         self.tokens.copy_(nxt)
         self.positions.add_(1)
@@ -411,24 +416,29 @@ class DecodeSession:
     def start(self, first_tokens: torch.Tensor) -> None:
         """first_tokens: the token chosen from the prefill logits (new token 0 of every sequence)."""
         self.tokens.copy_(first_tokens)
+        if self.seen is not None:
+            self.seen.scatter_(1, first_tokens[:, None], True)
         self.positions.copy_(self.prompt_lens)
         self.seqlens.copy_(self.prompt_lens + 1)
         self.out_tokens[0].copy_(first_tokens)
         self.step_idx.fill_(1)
         if self.use_graph and self.graph is None:
-            state = [t.clone() for t in (self.tokens, self.positions, self.seqlens, self.out_tokens, self.step_idx)]
+            live = [self.tokens, self.positions, self.seqlens, self.out_tokens, self.step_idx]
+            if self.seen is not None:
+                live.append(self.seen)
+            state = [t.clone() for t in live]
             side = torch.cuda.Stream(device=self.engine.device)
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
                 self._body()  # warm-up: cuBLAS workspaces, kernel attributes (writes only cache slots >= prompt length)
             torch.cuda.current_stream().wait_stream(side)
-            for t, c in zip((self.tokens, self.positions, self.seqlens, self.out_tokens, self.step_idx), state):
+            for t, c in zip(live, state):
                 t.copy_(c)
             torch.cuda.synchronize()
             self.graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self.graph):
                 self._body()
-            for t, c in zip((self.tokens, self.positions, self.seqlens, self.out_tokens, self.step_idx), state):
+            for t, c in zip(live, state):
                 t.copy_(c)  # capture does not execute, but keep the state explicit
 
     def step(self) -> None:
@@ -436,6 +446,19 @@ class DecodeSession:
             self.graph.replay()
         else:
             self._body()
+
+
+def greedy_pick(logits: torch.Tensor, ban: Optional[torch.Tensor], seen: Optional[torch.Tensor],
+                repetition_penalty: float) -> torch.Tensor:
+    """argmax of the processed last-row logits [B, vocab], as model.generate(do_sample=False) forms it: fp32 copy,
+    repetition penalty on the ids in `seen`, -inf on single-token bad words."""
+    if seen is not None and repetition_penalty != 1.0:
+        lf = logits.float()
+        logits = torch.where(seen, torch.where(lf < 0, lf * repetition_penalty, lf / repetition_penalty), lf)
+    if ban is not None:
+        logits[:, ban] = float("-inf")
+    nxt = logits.argmax(-1)
+    return nxt
 
 
 def packed_positions(cu_seqlens: torch.Tensor, n_rows: int) -> torch.Tensor:

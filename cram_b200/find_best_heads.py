@@ -61,23 +61,55 @@ def _model_dir_name(LLM: str) -> str:
     raise UnboundLocalError("cannot access local variable 'model_name'")  # the reference's failure mode
 
 
+def _dist_of(model):
+    """(rank, world_size, group) of a sharded Find_Best_Heads (its IESweep carries them); (0, 1, None) otherwise."""
+    sw = getattr(model, "sweep", None)
+    return int(getattr(sw, "rank", 0)), int(getattr(sw, "world_size", 1)), getattr(sw, "group", None)
+
+
+def _load_resume_state(file_path: str, rank: int, world: int, group):
+    """The reference's resume rule (:30-35) under torchrun: RANK 0 reads heads_scores.json and every rank gets ITS view
+    (one broadcast), so that all ranks skip the same samples and stay in step for cal_logits' all_gather."""
+    state = []
+    if rank == 0 and os.path.exists(file_path):
+        with open(file_path, "r", encoding="utf8") as file:
+            state = json.load(file)
+    if world > 1:
+        import torch.distributed as dist
+        box = [state]
+        dist.broadcast_object_list(box, src=0, group=group)
+        state = box[0]
+    return state
+
+
+def _write_json_rank0(obj, folder: str, file_path: str, rank: int) -> None:
+    """Only rank 0 writes (every rank holds the same matrix after the all_gather); temp file + os.replace so that a
+    reader -- or a restart after a kill -- never sees a truncated file."""
+    if rank != 0:
+        return
+    os.makedirs(folder, exist_ok=True)
+    tmp = file_path + ".tmp"
+    with open(tmp, "w", encoding="utf8") as file:
+        json.dump(obj, file, ensure_ascii=False, indent=4)
+    os.replace(tmp, file_path)
+
+
 def casual_tracing_per_head(filepath: str = "nq_100_bge.json", LLM: str = "Meta-Llama-3-8B-Instruct",
                             output_dir: str = "datasets/nq", contexts_type: list = ["ori_fake", "reranked_dense"],
                             topk: int = 4, model=None):
-    """utils/find_best_heads.py:13-58. `model` lets a caller pass a ready Find_Best_Heads (no hub access here)."""
+    """utils/find_best_heads.py:13-58. `model` lets a caller pass a ready Find_Best_Heads (no hub access here).
+    Under torchrun (a Find_Best_Heads built with rank / world_size) every rank runs this same loop: rank 0 owns the
+    file, the resume state is broadcast from it, and every rank returns the same list."""
     with open(filepath, "r", encoding="utf-8") as f:
         data = json.load(f)
     model_name = _model_dir_name(LLM)
     folder = os.path.join(output_dir, model_name)
     file_path = os.path.join(folder, "heads_scores.json")
-    if os.path.exists(file_path):
-        with open(file_path, "r", encoding="utf8") as file:
-            all_prob_changes = json.load(file)
-    else:
-        all_prob_changes = []
     if model is None:
         from .re_weighting import Find_Best_Heads
         model = Find_Best_Heads(model_name=LLM)
+    rank, world, group = _dist_of(model)
+    all_prob_changes = _load_resume_state(file_path, rank, world, group)
     for idx, sample in enumerate(data):
         if idx < len(all_prob_changes):  # resume rule: skip what the file already holds
             continue
@@ -91,9 +123,7 @@ def casual_tracing_per_head(filepath: str = "nq_100_bge.json", LLM: str = "Meta-
         prob_change = model.cal_logits(question=sample["question"], paras=contexts, scores=scores,
                                        wrong_answer=sample["wrong answer"])
         all_prob_changes.append(prob_change)
-        os.makedirs(folder, exist_ok=True)
-        with open(file_path, "w", encoding="utf8") as file:
-            json.dump(all_prob_changes, file, ensure_ascii=False, indent=4)
+        _write_json_rank0(all_prob_changes, folder, file_path, rank)
     return all_prob_changes
 
 
@@ -109,6 +139,7 @@ def casual_tracing_per_head_with_position(filepath: str = "nq_100_bge.json", LLM
         model = Find_Best_Heads(model_name=LLM)
     all_prob_changes = []
     folder = os.path.join(output_dir, model_name)
+    rank, _, _ = _dist_of(model)
     for sample in data:
         per_position = []
         ori_fake = sample["ori_fake"]
@@ -127,7 +158,5 @@ def casual_tracing_per_head_with_position(filepath: str = "nq_100_bge.json", LLM
             per_position.append(model.cal_logits(question=sample["question"], paras=contexts, scores=scores,
                                                  wrong_answer=sample["wrong answer"]))
         all_prob_changes.append(per_position)
-        os.makedirs(folder, exist_ok=True)
-        with open(os.path.join(folder, "heads_scores_pos.json"), "w", encoding="utf8") as file:
-            json.dump(all_prob_changes, file, ensure_ascii=False, indent=4)
+        _write_json_rank0(all_prob_changes, folder, os.path.join(folder, "heads_scores_pos.json"), rank)
     return all_prob_changes

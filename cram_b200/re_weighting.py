@@ -42,9 +42,12 @@ def _heads_dict_to_masks(layers_to_be_modified: dict, num_layers: int) -> List[i
 class Re_Weighting_Strategy:
 
     def __init__(self, model_name: str = "Llama-2-13b-chat-hf", layers_to_be_modified: dict = dict(), bad_words_ids=[],
-                 *, tokenizer=None, model=None, engine: Optional[CramEngine] = None, device: str = "cuda"):
+                 *, tokenizer=None, model=None, engine: Optional[CramEngine] = None, device: str = "cuda",
+                 generation_config=None):
         """Reference signature (utils/re_weighting.py:24). The keyword-only extras let a caller hand in an
-        already-loaded tokenizer / HF model / engine (the reference always loads by name, which needs the hub)."""
+        already-loaded tokenizer / HF model / engine (the reference always loads by name, which needs the hub).
+        ``generation_config`` defaults to ``model.generation_config``: model.generate(do_sample=False) at :132 still
+        applies its eos_token_id list and repetition_penalty (the Qwen chat checkpoints ship both)."""
         if not torch.cuda.is_available():
             raise ops.CramError("Re_Weighting_Strategy needs a CUDA device: cram_b200 has no CPU fallback")
         if tokenizer is None:
@@ -57,6 +60,7 @@ class Re_Weighting_Strategy:
                 model = AutoModelForCausalLM.from_pretrained(model_name, torch_dtype="auto")
             engine = CramEngine.from_hf_model(model, device=device)
         self.model = model  # HF module (config / weights source); the forward runs in self.engine
+        self.generation_config = generation_config if generation_config is not None else getattr(model, "generation_config", None)
         self.engine = engine
         self.model_name = model_name
         self.bad_words_ids = bad_words_ids
@@ -167,12 +171,7 @@ class Re_Weighting_Strategy:
     def decode_with_special_attention(self, question: str = "", paras: list = [], scores: list = [], answer: str = ""):
         """utils/re_weighting.py:63-113. Returns (model_inputs, attention_weight fp16 [1, T]) on the GPU."""
         r = self.span_index_batch([question], [paras], [scores], [answer])
-        e = int(r["err"][0].item())
-        if e & 1:
-            # a passage was not found verbatim in the prompt: the reference fails at :111 with this error
-            raise TypeError("unsupported operand type(s) for +: 'NoneType' and 'int'")
-        if e & 2:
-            raise RuntimeError("Trying to create tensor with negative dimension")
+        self._raise_on_span_errors([int(r["err"][0].item())])
         T = r["lens"][0]
         model_inputs = {"input_ids": r["input_ids"].view(1, T),
                         "attention_mask": torch.ones(1, T, dtype=torch.int64, device=r["input_ids"].device)}
@@ -181,10 +180,30 @@ class Re_Weighting_Strategy:
 
     # ---- generation -----------------------------------------------------------------------------------
     def _eos_ids(self) -> List[int]:
-        eos = [self.tokenizer.eos_token_id] if self.tokenizer.eos_token_id is not None else []
-        if self.model_name.find("Llama-3") != -1:  # utils/re_weighting.py:130-131
-            eos.append(self.tokenizer.convert_tokens_to_ids("<|eot_id|>"))
-        return eos
+        """Stop tokens of model.generate at utils/re_weighting.py:132. Llama-3: the explicit pair of :130-131, which
+        overrides the checkpoint's own list. Every other model: generation_config.eos_token_id (int or list) -- the
+        tokenizer's eos is only the fallback for an engine built without a HF model."""
+        if self.model_name.find("Llama-3") != -1:
+            return [self.tokenizer.eos_token_id, self.tokenizer.convert_tokens_to_ids("<|eot_id|>")]
+        gc_eos = getattr(self.generation_config, "eos_token_id", None)
+        if gc_eos is not None:
+            return [int(e) for e in (gc_eos if isinstance(gc_eos, (list, tuple)) else [gc_eos])]
+        return [self.tokenizer.eos_token_id] if self.tokenizer.eos_token_id is not None else []
+
+    def _repetition_penalty(self) -> float:
+        rp = getattr(self.generation_config, "repetition_penalty", None)
+        return float(rp) if rp is not None else 1.0
+
+    @staticmethod
+    def _raise_on_span_errors(errs) -> None:
+        """err bits of cram_span_index (include/cram_b200.h) -> the reference's exception classes."""
+        if any(e & 1 for e in errs):
+            # a passage was not found verbatim in the prompt: the reference fails at :111 with this error
+            raise TypeError("unsupported operand type(s) for +: 'NoneType' and 'int'")
+        if any(e & 2 for e in errs):
+            raise RuntimeError("Trying to create tensor with negative dimension")
+        if any(e & 4 for e in errs):
+            raise ops.CramError("more passages in one prompt than cram_span_index supports; the tail would be un-weighted")
 
     def _bad_tokens(self) -> List[int]:
         out = []
@@ -203,15 +222,14 @@ class Re_Weighting_Strategy:
     def run_RAG_batch(self, questions, paras_list, scores_list, max_new_tokens: int = 100):
         """Extension: per-sample credibility for a batch; equals the reference looped at b=1."""
         r = self.span_index_batch(questions, paras_list, scores_list)
-        errs = r["err"].tolist()
-        if any(e & 1 for e in errs):
-            raise TypeError("unsupported operand type(s) for +: 'NoneType' and 'int'")
+        self._raise_on_span_errors(r["err"].tolist())
         masks = _heads_dict_to_masks(self.layers_to_be_modified, self.num_hidden_layers)
         cu = np.cumsum([0] + r["lens"])
         prompts_ids = [r["input_ids"][cu[b]:cu[b + 1]] for b in range(len(questions))]
         logcreds = [r["logcred"][cu[b]:cu[b + 1]] for b in range(len(questions))]
         new = self.engine.generate(prompts_ids, logcreds, masks, max_new_tokens=max_new_tokens,
-                                   eos_token_ids=self._eos_ids(), bad_token_ids=self._bad_tokens())
+                                   eos_token_ids=self._eos_ids(), bad_token_ids=self._bad_tokens(),
+                                   repetition_penalty=self._repetition_penalty())
         results = []
         for b in range(len(questions)):
             full = prompts_ids[b].tolist() + new[b]

@@ -150,13 +150,53 @@ def train_tokenizer(path: str = TOKENIZER_JSON, vocab_size: int = 1000) -> str:
     return path
 
 
-def load_tokenizer(path: str = TOKENIZER_JSON):
-    """The committed tokenizer wrapped as a HF fast tokenizer (gives real ``offset_mapping``)."""
+# The public chat templates of the two model families the reference special-cases
+# (/root/reference/utils/re_weighting.py:64-95). Llama-3-Instruct: the template itself emits the BOS token, so that
+# tokenising the rendered string with add_special_tokens=True (:98) yields a DOUBLE BOS; the message content is
+# trimmed. Qwen (ChatML): no BOS anywhere, the reference tokenises with add_special_tokens=False (:93).
+LLAMA3_CHAT_TEMPLATE = (
+    "{% set loop_messages = messages %}{% for message in loop_messages %}"
+    "{% set content = '<|start_header_id|>' + message['role'] + '<|end_header_id|>\n\n'+ message['content'] | trim + '<|eot_id|>' %}"
+    "{% if loop.index0 == 0 %}{% set content = bos_token + content %}{% endif %}{{ content }}{% endfor %}"
+    "{% if add_generation_prompt %}{{ '<|start_header_id|>assistant<|end_header_id|>\n\n' }}{% endif %}")
+QWEN_CHAT_TEMPLATE = (
+    "{% for message in messages %}{% if loop.first and messages[0]['role'] != 'system' %}"
+    "{{ '<|im_start|>system\nYou are a helpful assistant.<|im_end|>\n' }}{% endif %}"
+    "{{'<|im_start|>' + message['role'] + '\n' + message['content'] + '<|im_end|>' + '\n'}}{% endfor %}"
+    "{% if add_generation_prompt %}{{ '<|im_start|>assistant\n' }}{% endif %}")
+LLAMA3_SPECIALS = ["<|start_header_id|>", "<|end_header_id|>", "<|eot_id|>"]
+QWEN_SPECIALS = ["<|im_start|>", "<|im_end|>", "<|endoftext|>"]
+CHAT_VOCAB = 1008  # 1000 BPE entries + room for the added special tokens (embedding rows of the chat test models)
+
+
+def load_tokenizer(path: str = TOKENIZER_JSON, kind: str = "raw"):
+    """The committed tokenizer wrapped as a HF fast tokenizer (gives real ``offset_mapping``).
+
+    ``kind``: "raw" -- BOS ``<s>`` prepended by the post-processor, no chat template (the reference's Llama-2 / else
+    branch); "llama3" -- the same BOS post-processor plus the Llama-3 header / ``<|eot_id|>`` special tokens and chat
+    template (double BOS under add_special_tokens=True); "qwen" -- ChatML special tokens and template, NO BOS
+    post-processor, eos ``<|im_end|>`` (so ``tokenizer([answer]).input_ids[0, 1:]`` drops a real token,
+    /root/reference/utils/re_weighting.py:155). The BPE vocabulary (ids 0..999) is shared by all three.
+    """
     from transformers import PreTrainedTokenizerFast
 
     if not os.path.exists(path):
         raise FileNotFoundError(f"{path} missing: run `python -m cram_b200.synth` to train it")
-    return PreTrainedTokenizerFast(tokenizer_file=path, bos_token="<s>", eos_token="</s>", pad_token="<pad>")
+    if kind == "raw":
+        return PreTrainedTokenizerFast(tokenizer_file=path, bos_token="<s>", eos_token="</s>", pad_token="<pad>")
+    from tokenizers import AddedToken, Tokenizer, processors
+
+    tok = Tokenizer.from_file(path)
+    if kind == "llama3":
+        tok.add_special_tokens([AddedToken(t, special=True, normalized=False) for t in LLAMA3_SPECIALS])
+        return PreTrainedTokenizerFast(tokenizer_object=tok, bos_token="<s>", eos_token="</s>", pad_token="<pad>",
+                                       chat_template=LLAMA3_CHAT_TEMPLATE)
+    if kind == "qwen":
+        tok.add_special_tokens([AddedToken(t, special=True, normalized=False) for t in QWEN_SPECIALS])
+        tok.post_processor = processors.ByteLevel(trim_offsets=False)
+        return PreTrainedTokenizerFast(tokenizer_object=tok, eos_token="<|im_end|>", pad_token="<|endoftext|>",
+                                       chat_template=QWEN_CHAT_TEMPLATE)
+    raise ValueError(f"unknown tokenizer kind {kind!r}")
 
 
 def sample_with_token_target(tokenizer, seed: int, n_docs: int, target_tokens: int, build_prompt,

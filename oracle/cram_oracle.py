@@ -10,7 +10,7 @@ Parity status: PINNED. ``oracle/make_golden.py`` imports the unmodified referenc
 inputs, asserts equality (bit-exact for indices / fp16 credibility / ranking, max-abs 0 for fp32
 logits on the tiny model) and writes the fixtures under ``tests/golden/``. The ranking functions are
 additionally pinned by the reference's own shipped artefacts (``datasets/*/*/heads_scores*.json``,
-``selected_heads.json``), see ``tests/test_ranking_kat.py``.
+``selected_heads.json``), see ``tests/test_oracle_golden.py::test_ranking_kat``.
 
 Every function cites the reference lines it follows (paths relative to /root/reference). The model
 arithmetic itself lives in HF transformers (un-pinned by the reference; 5.5.0 installed here):
@@ -119,10 +119,11 @@ def edit_attention_mask(mask: Optional[torch.Tensor], logcred: torch.Tensor, hea
     """
     weight_len = logcred.shape[-1]
     if mask is None:
+        dev = logcred.device  # the reference builds it on hidden_states.device (:38); callers keep logcred there
         if tgt_len == 1:
-            mask = torch.zeros([1, 1, tgt_len, src_len], dtype=dtype)
+            mask = torch.zeros([1, 1, tgt_len, src_len], dtype=dtype, device=dev)
         else:
-            m = torch.triu(torch.full((tgt_len, src_len), torch.finfo(dtype).min, dtype=dtype), diagonal=1)
+            m = torch.triu(torch.full((tgt_len, src_len), torch.finfo(dtype).min, dtype=dtype, device=dev), diagonal=1)
             mask = m[None, None]
     else:
         mask = mask.clone()
@@ -323,10 +324,15 @@ def cal_logits(sd, spec: ModelSpec, input_ids: torch.Tensor, logcred: torch.Tens
 
 
 def greedy_generate(sd, spec: ModelSpec, input_ids: torch.Tensor, hooks, max_new_tokens: int,
-                    eos_ids: Sequence[int] = ()) -> List[int]:
+                    eos_ids: Sequence[int] = (), repetition_penalty: float = 1.0, bad_ids: Sequence[int] = ()) -> List[int]:
     """utils/re_weighting.py:126-132 (do_sample=False). Re-runs the full prefix each step: with the
     hook's :57 rule (bias only on key columns < T0 where the mask is 0) a cached decode step and a
-    full recompute give the same probabilities, so this is the simplest faithful restatement."""
+    full recompute give the same probabilities, so this is the simplest faithful restatement.
+
+    ``repetition_penalty`` != 1 restates what model.generate still applies from the checkpoint's generation_config
+    under do_sample=False (transformers generation/logits_process.py, RepetitionPenaltyLogitsProcessor: on the fp32 copy
+    of the last-row logits, every token id already in the sequence -- prompt included -- gets logit*p if negative,
+    logit/p otherwise); ``bad_ids`` are single-token bad_words_ids (NoBadWordsLogitsProcessor: -inf)."""
     ids = input_ids.clone()
     new = []
     for _ in range(max_new_tokens):
@@ -337,7 +343,14 @@ def greedy_generate(sd, spec: ModelSpec, input_ids: torch.Tensor, hooks, max_new
             ext = torch.zeros(1, T, dtype=lc.dtype)
             ext[:, :T0] = lc
             hk[l] = (ext, heads)
-        nxt = int(llama_forward(sd, spec, ids, hk)[0, -1].argmax())
+        row = llama_forward(sd, spec, ids, hk)[0, -1].to(torch.float32)
+        if repetition_penalty != 1.0:
+            seen = ids[0].unique()
+            sc = row[seen]
+            row[seen] = torch.where(sc < 0, sc * repetition_penalty, sc / repetition_penalty)
+        for b in bad_ids:
+            row[b] = float("-inf")
+        nxt = int(row.argmax())
         new.append(nxt)
         ids = torch.cat([ids, torch.tensor([[nxt]])], dim=1)
         if nxt in eos_ids:

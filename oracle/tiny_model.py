@@ -52,6 +52,28 @@ def tiny_state_dict(dtype=torch.float32) -> Dict[str, torch.Tensor]:
     return random_state_dict(TINY_SPEC, seed=0, dtype=dtype)
 
 
+CHAT_VOCAB = 1008  # cram_b200.synth.CHAT_VOCAB: 1000 BPE ids + the chat special tokens
+
+
+def chat_spec(kind: str) -> ModelSpec:
+    """The tiny model of the chat-template fixtures: TINY_SPEC with room for the special tokens; "qwen" is a Qwen2
+    (QKV bias)."""
+    return ModelSpec(num_layers=2, num_heads=4, num_kv_heads=2, head_dim=64, hidden=256, intermediate=512,
+                     vocab=CHAT_VOCAB, rms_eps=1e-5 if kind == "llama3" else 1e-6, rope_theta=10000.0,
+                     qkv_bias=(kind == "qwen"))
+
+
+def chat_state_dict(kind: str, meta: dict = None, dtype=torch.float32) -> Dict[str, torch.Tensor]:
+    """Seeded weights of the chat fixtures. With ``meta`` (tests/golden/chat_model_meta.json[kind]) the <|eot_id|>
+    rigging recorded by oracle/make_golden_chat.py:rig_eot is re-applied, in fp32 before the cast."""
+    sd = random_state_dict(chat_spec(kind), seed={"llama3": 21, "qwen": 22}[kind])
+    if meta is not None and "eot_src_token" in meta:
+        from cram_b200 import synth
+        eot = 1000 + synth.LLAMA3_SPECIALS.index("<|eot_id|>")
+        sd["lm_head.weight"][eot] = sd["lm_head.weight"][meta["eot_src_token"]] * meta["eot_scale"]
+    return {k: v.to(dtype) for k, v in sd.items()}
+
+
 def hf_model_from(spec: ModelSpec, sd: Dict[str, torch.Tensor], attn: str = "eager"):
     """A HF LlamaForCausalLM / Qwen2ForCausalLM carrying ``sd`` (eager attention = the reference path)."""
     from transformers import LlamaConfig, LlamaForCausalLM, Qwen2Config, Qwen2ForCausalLM

@@ -45,6 +45,10 @@ SM100_CASES = [
     ([1, 127, 129, 500, 64], 8, 2, 128),
     ([1000, 77], 4, 1, 64),
     ([2048], 8, 2, 128),
+    ([300, 129], 64, 8, 128),     # Llama-3-70B heads: GQA group of 8, head_mask bits >= 32
+    ([515, 64], 28, 4, 128),      # Qwen2-7B heads: GQA group of 7
+    ([257], 40, 40, 128),         # Llama-2-13B heads (MHA), bits >= 32
+    ([8192], 4, 1, 128),          # T >> 2048: 64 key tiles per row block, 32 CTAs per head
 ]
 
 
@@ -55,7 +59,8 @@ def test_sm100_vs_reference(lens, H, Hkv, dh, dtype):
     q, k, v, _ = make_qkv(total, H, Hkv, dh, dtype, DEV, seed=5)
     cu = cu_of(lens, DEV)
     lc = make_logcred(lens, DEV, dtype, seed=6)
-    for mask in (0, 0b10, (1 << H) - 1):
+    # no head / one low head / highest + middle + lowest head (bits >= 32 when H > 32) / all heads
+    for mask in (0, 0b10, (1 << (H - 1)) | (1 << (H // 2)) | 1, (1 << H) - 1):
         got, lse = ops.attn_prefill(q, k, v, cu, max(lens), H, Hkv, dh, logcred=lc, head_mask=mask, kernel=SM100,
                                     return_lse=True)
         want = ref_attention(q, k, v, cu, None, H, Hkv, dh, logcred=lc, head_mask=mask)

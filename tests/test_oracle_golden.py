@@ -122,3 +122,58 @@ def test_cached_decode_step_equals_full_recompute():
                 ext[:, :T0] = lc[:, :t + 1][:, :T0]
                 full = orc.llama_forward(sd, spec, ids[:, :t + 1], {l: (ext, h) for l, (_, h) in hooks.items()})[0, -1]
                 assert torch.allclose(step[0], full, atol=2e-5, rtol=1e-5), t
+
+
+def test_chat_template_branches_oracle_vs_reference_golden(golden_dir):
+    """Llama-3 / Qwen branches of utils/re_weighting.py:64-97 (fixtures: oracle/make_golden_chat.py, from the unmodified
+    reference): prompt construction + tokenisation + span index bit-exact, greedy tokens incl. the dual-EOS stop and the
+    generation_config repetition penalty, one IE entry, and the Qwen 'first real answer token dropped' quirk."""
+    from cram_b200 import synth
+    from oracle.tiny_model import chat_spec, chat_state_dict
+    g = np.load(os.path.join(golden_dir, "chat_model.npz"))
+    meta = json.load(open(os.path.join(golden_dir, "chat_model_meta.json")))
+    for name in ("llama3", "qwen"):
+        m = meta[name]
+        tok = synth.load_tokenizer(kind=m["kind"])
+        for ci, c in enumerate(m["cases"]):
+            prompt, ast = orc.build_prompt(tok, m["model_name"], c["question"], c["paras"], c["answer"])
+            enc = tok([prompt], return_offsets_mapping=True, add_special_tokens=ast)
+            assert np.array_equal(np.array(enc["input_ids"][0]), g[f"{name}_case{ci}_ids"]), (name, ci)
+            off = np.array(enc["offset_mapping"][0], dtype=np.int64)[:, 0]
+            doc_id, cred = orc.span_index(off, orc.char_spans(prompt, c["paras"]), c["scores"])
+            assert np.array_equal(cred.view(np.uint16), g[f"{name}_case{ci}_cred_bits"]), (name, ci)
+            assert np.array_equal(doc_id, g[f"{name}_case{ci}_doc_id"]), (name, ci)
+        ids0 = g[f"{name}_case0_ids"]
+        if name == "llama3":
+            assert ids0[0] == ids0[1] == tok.bos_token_id  # template BOS + add_special_tokens BOS (:77 + :98)
+        else:
+            assert ids0[0] == tok.convert_tokens_to_ids("<|im_start|>")  # no BOS at all (:93)
+        # generation: one hooked head set per branch on the CPU (all four run on the GPU against the same fixture)
+        spec, sd = chat_spec(m["kind"]), chat_state_dict(m["kind"], m)
+        prompt, ast = orc.build_prompt(tok, m["model_name"], m["question"], m["paras"], "")
+        enc = tok([prompt], return_offsets_mapping=True, add_special_tokens=ast)
+        ids = torch.tensor(enc["input_ids"])
+        off = np.array(enc["offset_mapping"][0], dtype=np.int64)[:, 0]
+        _, cred = orc.span_index(off, orc.char_spans(prompt, m["paras"]), m["scores"])
+        lc = orc.log_chain(cred, torch.float32)[None]
+        eos = ([tok.eos_token_id, tok.convert_tokens_to_ids("<|eot_id|>")] if name == "llama3" else m["eos_token_id"])
+        with torch.no_grad():
+            for hs_name, hooks in (("none", {}), ("all", {0: (lc, [0, 1, 2, 3]), 1: (lc, [0, 1, 2, 3])})):
+                toks = orc.greedy_generate(sd, spec, ids, hooks, m["max_new"], eos_ids=eos,
+                                           repetition_penalty=m.get("repetition_penalty", 1.0))
+                assert toks == g[f"{name}_gen_{hs_name}"].tolist(), (name, hs_name)
+            if name == "llama3":  # stopped early, on the SECOND id of the dual-EOS list (:130-131)
+                assert g["llama3_gen_none"][-1] == eos[1] and len(g["llama3_gen_none"]) < m["max_new"]
+            ids2 = torch.from_numpy(g[f"{name}_ie_input_ids"])[None]
+            lc2 = orc.log_chain(g[f"{name}_ie_cred_bits"].view(np.float16), torch.float32)[None]
+            ans = torch.from_numpy(g[f"{name}_ie_answer_ids"])
+            ori = orc.answer_logit_sum(orc.llama_forward(sd, spec, ids2), ans)
+            assert abs(float(ori) - float(g[f"{name}_ie_ori_logit_sum"])) <= 2e-4
+            cur = orc.answer_logit_sum(orc.llama_forward(sd, spec, ids2, {0: (lc2, [3])}), ans)
+            assert abs(float(ori - cur) - g[f"{name}_ie_ref"][0, 3]) <= 2e-4
+        full = tok([m["wrong"]])["input_ids"][0]
+        if name == "qwen":   # :155 drops a REAL token when the tokenizer adds no BOS
+            assert g["qwen_ie_answer_ids"].tolist() == full[1:] and len(full) == len(g["qwen_ie_answer_ids"]) + 1
+            assert full[0] != tok.convert_tokens_to_ids("<|im_start|>")
+        else:                # :155 drops the BOS
+            assert full[0] == tok.bos_token_id and g["llama3_ie_answer_ids"].tolist() == full[1:]
