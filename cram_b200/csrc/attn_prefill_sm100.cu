@@ -92,6 +92,36 @@ __device__ __forceinline__ float ex2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// Timing ablations (scripts/dev/variants.py builds separate libraries with these; results are WRONG on purpose, the
+// product build defines none): a share of the exponentials is replaced by one FMA-pipe instruction to measure how far
+// the kernel is from the point where the MUFU pipe stops mattering.
+__device__ __forceinline__ float ex2_fake(float x) { return fmaf(x, 0.001f, 0.5f); }
+#if defined(CRAM_ABL_NOEXP)
+#define CRAM_EX2_0 ex2_fake
+#define CRAM_EX2_1 ex2_fake
+#define CRAM_EX2_2 ex2_fake
+#define CRAM_EX2_3 ex2_fake
+#elif defined(CRAM_ABL_QUARTEREXP)
+#define CRAM_EX2_0 ex2
+#define CRAM_EX2_1 ex2_fake
+#define CRAM_EX2_2 ex2_fake
+#define CRAM_EX2_3 ex2_fake
+#elif defined(CRAM_ABL_HALFEXP)
+#define CRAM_EX2_0 ex2
+#define CRAM_EX2_1 ex2_fake
+#define CRAM_EX2_2 ex2
+#define CRAM_EX2_3 ex2_fake
+#elif defined(CRAM_ABL_3QEXP)
+#define CRAM_EX2_0 ex2
+#define CRAM_EX2_1 ex2
+#define CRAM_EX2_2 ex2
+#define CRAM_EX2_3 ex2_fake
+#else
+#define CRAM_EX2_0 ex2
+#define CRAM_EX2_1 ex2
+#define CRAM_EX2_2 ex2
+#define CRAM_EX2_3 ex2
+#endif
 // packed fp32x2 arithmetic (FFMA2 / FADD2): two lanes per issue slot
 __device__ __forceinline__ uint64_t pk2(float lo, float hi) {
   uint64_t r;
@@ -203,7 +233,7 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
       float e0, e1, e2, e3;
       upk2(fadd2(t01, negm_spec), e0, e1);
       upk2(fadd2(t23, negm_spec), e2, e3);
-      const float p0 = ex2(e0), p1 = ex2(e1), p2 = ex2(e2), p3 = ex2(e3);
+      const float p0 = CRAM_EX2_0(e0), p1 = CRAM_EX2_1(e1), p2 = CRAM_EX2_2(e2), p3 = CRAM_EX2_3(e3);
       la = fadd2(la, pk2(p0, p1));
       lb = fadd2(lb, pk2(p2, p3));
       pk[c * 16 + i / 2 + 0] = pack2<T>(p0, p1);
@@ -256,7 +286,7 @@ __device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32
         float e0, e1, e2, e3;
         upk2(fadd2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), negm), e0, e1);
         upk2(fadd2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), negm), e2, e3);
-        const float p0 = ex2(e0), p1 = ex2(e1), p2 = ex2(e2), p3 = ex2(e3);
+        const float p0 = CRAM_EX2_0(e0), p1 = CRAM_EX2_1(e1), p2 = CRAM_EX2_2(e2), p3 = CRAM_EX2_3(e3);
         la = fadd2(la, pk2(p0, p1));
         lb = fadd2(lb, pk2(p2, p3));
         pk[c * 16 + i / 2 + 0] = pack2<T>(p0, p1);

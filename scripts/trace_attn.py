@@ -20,10 +20,10 @@ def build(block, extra=(), out=OUT):
     print("built", out)
 
 def run():
-    os.environ["CRAM_B200_LIB"] = OUT
+    os.environ["CRAM_B200_LIB"] = os.environ.get("TRACE_LIB", OUT)
     import numpy as np, torch
     from cram_b200 import ops, _lib
-    B, T, H, Hkv, dh = 16, 2048, 32, 8, 128
+    B, T, H, Hkv, dh = int(os.environ.get("TRACE_B", 16)), int(os.environ.get("TRACE_T", 2048)), 32, 8, 128
     dev = "cuda"
     g = torch.Generator(device=dev).manual_seed(0)
     lens = [T - 3 * i for i in range(B)]
