@@ -1,8 +1,11 @@
-// Kernel (1): fused credibility-biased FlashAttention-style prefill for sm_100a (v2: two query tiles
-// per CTA, ping-pong softmax warpgroups).
+// Kernel (1): fused credibility-biased FlashAttention-style prefill for sm_100a (v5: two query tiles
+// per CTA, ping-pong softmax warpgroups, 128-key tiles).
 //
-//   S = Q K^T      tcgen05.mma (SS), 128x128 fp32 accumulator in TMEM, operands TMA-staged in
-//                  128B-swizzled shared memory
+//   S = Q K^T      tcgen05.mma (SS) M128 x N128 x K16, 128x128 fp32 accumulator in TMEM, operands TMA-staged in
+//                  128B-swizzled shared memory. N = 128 is what keeps this product off the shared-memory read port:
+//                  every instruction re-reads its 4 KB slice of Q whatever N is, so at N = 64 (v4) the pair of operands
+//                  needed 192 B/clk of a 128 B/clk port and Q K^T ran at 2/3 of the tensor rate
+//                  (profiles/r2_attn_ablation_and_trace.md); at N = 128 it is 8 KB per 64 cycles = 128 B/clk
 //   online softmax one thread per query row straight out of TMEM (tcgen05.ld 32x32b); the per-key
 //                  log-credibility bias (already x log2e, with the key-length mask folded in as
 //                  -inf) is one packed FFMA2: t = S*scale*log2e + bias[k]
@@ -19,14 +22,16 @@
 //   warps 4-7   same for stage 1
 //   warp  8     producer: TMA loads of Q0, Q1, K[j], V[j]
 //   warp  9     MMA issuer (one elected lane); owns the TMEM allocation
-//   warp  10    builds the per-tile bias vectors (log-credibility x log2e, -inf past the key length), 4 tiles ahead
+//   warp  10    builds the per-tile bias vectors (log-credibility x log2e, -inf past the key length), 2 tiles ahead
 //   warp  11    idle (warps 8-11 exist so that setmaxnreg can hand their registers to the softmax warps)
 // The two stages share every K/V tile (half the shared-memory traffic per FLOP of a one-tile CTA) and
 // alternate on the tensor pipe: while warpgroup s runs the softmax of tile j, the MMA warp runs
-// P V (j) and Q K^T (j+1) of the other stage. TMEM: S0 | S1 | O0 | O1 (4 x 128 columns); P aliases S.
+// P V (j) and Q K^T (j+1) of the other stage. TMEM: S0 | S1 | O0 | O1 (4 x 128 columns); P (64 packed columns)
+// aliases the first half of S, so per stage the chain is softmax(j) -> P V(j) -> Q K^T(j+1) -> softmax(j+1).
 // Lazy O rescale (only when a row's max grows by more than 2^8) keeps the correction off the hot loop, and lets the
 // exponentials of a tile be issued speculatively against the standing reference max, in the pass that forms the scores.
 #include <mutex>
+#include <type_traits>
 #include <utility>
 
 #include "attn.cuh"
@@ -38,9 +43,9 @@ namespace {
 
 constexpr int kBlockM = 128;  // rows per query tile (= TMEM lanes)
 constexpr int kStages = 2;    // query tiles per CTA
-constexpr int kBlockN = 64;   // keys per K/V tile
-constexpr int kKV = 4;        // K ring depth = V ring depth
-constexpr int kBiasRing = 8;  // bias vectors in flight (written with K[j], read until P V[j] is done)
+constexpr int kBlockN = 128;  // keys per K/V tile
+constexpr int kKV = 2;        // K ring depth = V ring depth (32 KB per slot at d = 128)
+constexpr int kBiasRing = 4;  // bias vectors in flight (written with K[j], read until P V[j] is done)
 constexpr int kThreads = 384;
 constexpr int kTmemCols = 512;
 constexpr float kLog2e = 1.4426950408889634f;
@@ -49,13 +54,23 @@ constexpr float kRescaleThreshold = 8.0f;  // log2 units
 // build compiles none of this): clock64 stamps of one CTA's softmax warps, MMA issuer and producer, per tile.
 #ifdef CRAM_ATTN_TRACE
 __device__ long long g_trace[12][64][4];
+__device__ long long g_trace_fine[16][16];  // warp 0, tiles 16..31: stamps inside softmax_tile
+__device__ int g_trace_tile;
 #define CRAM_TRACE(slot, j, e)                                                              \
   do {                                                                                      \
     if (blockIdx.x == CRAM_ATTN_TRACE && (j) < 64) g_trace[slot][j][e] = clock64();         \
   } while (0)
+#define CRAM_TRACE_FINE(e)                                                                                   \
+  do {                                                                                                       \
+    if (blockIdx.x == CRAM_ATTN_TRACE && threadIdx.x == 0 && g_trace_tile >= 16 && g_trace_tile < 32)          \
+      g_trace_fine[g_trace_tile - 16][e] = clock64();                                                         \
+  } while (0)
 #else
 #define CRAM_TRACE(slot, j, e) \
   do {                         \
+  } while (0)
+#define CRAM_TRACE_FINE(e) \
+  do {                     \
   } while (0)
 #endif
 
@@ -64,7 +79,9 @@ struct Barriers {
   uint64_t k_full[kKV], k_empty[kKV];
   uint64_t v_full[kKV], v_empty[kKV];
   uint64_t bias_full[kBiasRing];
-  uint64_t s_full[2][2], p_full[2][2];  // [query stage][S buffer]
+  uint64_t s_full[2];                   // [query stage] S(j) is complete (one phase per tile)
+  uint64_t p_full[2][2];                // [query stage][half] P of that 64-key half is written (one phase per tile)
+  uint64_t o_half[2];                   // [query stage] P V of the first half has completed (exact path of the second)
   uint64_t o_done[2];                   // [query stage] one phase per P V (lazy-rescale wait)
   uint64_t o_final[2];                  // [query stage] single phase: the last P V has completed
 };
@@ -74,7 +91,7 @@ struct Smem {
   static constexpr int kQTileBytes = kBlockM * DH * 2;
   static constexpr int kQSlabBytes = kBlockM * 128;  // 128 rows x 64 elements (one 128B swizzle slab)
   static constexpr int kTileBytes = kBlockN * DH * 2;  // one K / V tile
-  static constexpr int kSlabBytes = kBlockN * 128;     // 64 rows x 64 elements
+  static constexpr int kSlabBytes = kBlockN * 128;     // 128 rows x 64 elements
   static constexpr int kQ = 0;
   static constexpr int kK = kQ + kStages * kQTileBytes;
   static constexpr int kV = kK + kKV * kTileBytes;
@@ -175,130 +192,164 @@ __device__ __forceinline__ uint32_t pack2<__half>(float lo, float hi) {
   return r;
 }
 
-// One K/V tile of one query row (= one thread): S from TMEM -> t = S*scale2 + bias[k] -> running max
-// (lazy rescale of O) -> P = 2^(t - m) packed to T and written back over the S columns.
+// ---- softmax of one K/V tile (128 keys) for one query row (= one thread) ----------------------------------------
+// t = S*scale2 + bias[k] (one packed FFMA2 per two scores; this is where the credibility enters), P = 2^(t - m_ref)
+// packed to T and written back over the first half of the S columns, in two 64-key halves with their own hand-off to
+// the MMA warp (P V of the first half runs under the softmax of the second).
+//
+// m_ref is the reference the exponentials are taken against. O / l does not depend on it; it only has to keep the numbers
+// in range, and bf16 / fp32 have 2^+-126 of it. So there is no running max in the hot loop at all: a half-tile is ONE
+// pass (scores -> exponentials -> row sum -> pack), and its row sum is the overflow detector:
+//   sum < 2^14        nothing to do (every p < 2^14: exact in bf16, inside the fp16 range);
+//   sum >= 2^14       "soft": the NEXT tile starts from m_ref + log2(sum) (>= the true max), after the main loop has
+//                     rescaled O and l -- lazy and delayed, off the hot path; fp16 P takes the exact path instead;
+//   sum = inf / NaN   some t - m_ref exceeded 127: exact two-pass path for this half (half max, rescale, recompute from
+//                     the scores, which are still intact in TMEM because P of a half is stored only after this check).
+// The first tile of a row block takes its reference from the max of its first 32 keys.
+template <typename T>
+struct ExactAbove {
+  static constexpr float value = 1.0e38f;  // bf16 P: only a non-finite sum needs the exact path
+};
+template <>
+struct ExactAbove<__half> {
+  static constexpr float value = 16384.0f;  // fp16 P saturates at 2^16
+};
+constexpr float kSoftAbove = 16384.0f;  // 2^14
+
 // kDiag: the tile straddles the causal diagonal, columns > climit are masked.
-template <typename T, int DH, bool kDiag>
-__device__ __forceinline__ void softmax_tile(const uint32_t s_addr, const uint32_t o_addr, const uint32_t bias,
-                                             const float scale2, const int climit, const bool first,
-                                             uint64_t* o_done_bar, const uint32_t o_done_parity, float& m_ref,
-                                             float& l) {
-  uint32_t s[2][32];
-  const uint64_t sc2 = pk2(scale2, scale2);
-  float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-  // Speculative exponentials: the reference max only moves when a tile beats it by more than 2^8 (lazy rescale), so
-  // almost every tile ends up using the m_ref it started with. The exps are therefore issued against that value in
-  // the SAME pass that forms the scores and the tile max -- the MUFU pipe runs under the FFMA2 / max stream instead
-  // of after it -- and are redone only if some row of the warp does move its reference (first tiles, rare later).
-  const float m_spec = (m_ref == -INFINITY) ? 0.f : m_ref;
-  const uint64_t negm_spec = pk2(-m_spec, -m_spec);
-  uint64_t la = pk2(0.f, 0.f), lb = pk2(0.f, 0.f);
-  uint32_t pk[32];
-  // TMEM -> registers in two 32-column chunks; the load of chunk c+1 is in flight while chunk c is processed.
-  ptx::tmem_ld32(s_addr, s[0]);
+template <bool kDiag>
+__device__ __forceinline__ void score_chunk(const uint32_t (&raw)[32], const uint32_t bias, const int c, const uint64_t sc2,
+                                            const int climit, float (&t)[32]) {
 #pragma unroll
-  for (int c = 0; c < 2; ++c) {
-    ptx::tc_wait_ld_regs(s[c]);
-    if (c + 1 < 2) ptx::tmem_ld32(s_addr + (c + 1) * 32, s[c + 1]);
+  for (int i = 0; i < 32; i += 4) {
+    uint64_t bx, by;
+    asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(bx), "=l"(by) : "r"(bias + (c * 32 + i) * 4));
+    const uint64_t t01 = ffma2(pk2(__uint_as_float(raw[i + 0]), __uint_as_float(raw[i + 1])), sc2, bx);
+    const uint64_t t23 = ffma2(pk2(__uint_as_float(raw[i + 2]), __uint_as_float(raw[i + 3])), sc2, by);
+    upk2(t01, t[i + 0], t[i + 1]);
+    upk2(t23, t[i + 2], t[i + 3]);
+    if (kDiag) {
+      const int col = c * 32 + i;
+      t[i + 0] = (col + 0 <= climit) ? t[i + 0] : -INFINITY;
+      t[i + 1] = (col + 1 <= climit) ? t[i + 1] : -INFINITY;
+      t[i + 2] = (col + 2 <= climit) ? t[i + 2] : -INFINITY;
+      t[i + 3] = (col + 3 <= climit) ? t[i + 3] : -INFINITY;
+    }
+  }
+}
+
+// max over the scores of chunks [c0, c1)
+template <bool kDiag>
+__device__ __forceinline__ float chunks_max(const uint32_t s_addr, const uint32_t bias, const uint64_t sc2, const int climit,
+                                            const int c0, const int c1) {
+  float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll 1
+  for (int c = c0; c < c1; ++c) {
+    uint32_t raw[32];
+    ptx::tmem_ld32(s_addr + c * 32, raw);
+    ptx::tc_wait_ld_regs(raw);
+    float t[32];
+    score_chunk<kDiag>(raw, bias, c, sc2, climit, t);
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
-      uint64_t bx, by;
-      asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(bx), "=l"(by) : "r"(bias + (c * 32 + i) * 4));
-      uint64_t t01 = ffma2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), sc2, bx);
-      uint64_t t23 = ffma2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), sc2, by);
-      float t0, t1, t2, t3;
-      upk2(t01, t0, t1);
-      upk2(t23, t2, t3);
-      if (kDiag) {
-        const int col = c * 32 + i;
-        t0 = (col + 0 <= climit) ? t0 : -INFINITY;
-        t1 = (col + 1 <= climit) ? t1 : -INFINITY;
-        t2 = (col + 2 <= climit) ? t2 : -INFINITY;
-        t3 = (col + 3 <= climit) ? t3 : -INFINITY;
-        t01 = pk2(t0, t1);
-        t23 = pk2(t2, t3);
-      }
-      s[c][i + 0] = __float_as_uint(t0);
-      s[c][i + 1] = __float_as_uint(t1);
-      s[c][i + 2] = __float_as_uint(t2);
-      s[c][i + 3] = __float_as_uint(t3);
-      if (i & 4) {
-        mx2 = fmax3(mx2, t0, t1);
-        mx3 = fmax3(mx3, t2, t3);
-      } else {
-        mx0 = fmax3(mx0, t0, t1);
-        mx1 = fmax3(mx1, t2, t3);
-      }
-#ifndef CRAM_NO_SPEC_SOFTMAX
+      mx0 = fmax3(mx0, t[i + 0], t[i + 1]);
+      mx1 = fmax3(mx1, t[i + 2], t[i + 3]);
+    }
+  }
+  return fmaxf(mx0, mx1);
+}
+
+// exact pass over chunks [c0, c1) against a known reference: P chunk c (16 packed columns) goes straight over S columns
+// [16c, 16c+16), which belong to chunks already consumed. Returns the row sum.
+template <typename T, bool kDiag>
+__device__ __forceinline__ float exact_pass(const uint32_t s_addr, const uint32_t bias, const uint64_t sc2, const int climit,
+                                            const float m_ref, const int c0, const int c1) {
+  const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
+  const uint64_t negm = pk2(-m_use, -m_use);
+  uint64_t la = pk2(0.f, 0.f), lb = pk2(0.f, 0.f);
+#pragma unroll 1
+  for (int c = c0; c < c1; ++c) {
+    uint32_t raw[32];
+    ptx::tmem_ld32(s_addr + c * 32, raw);
+    ptx::tc_wait_ld_regs(raw);
+    float t[32];
+    score_chunk<kDiag>(raw, bias, c, sc2, climit, t);
+    uint32_t pk[16];
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
       float e0, e1, e2, e3;
-      upk2(fadd2(t01, negm_spec), e0, e1);
-      upk2(fadd2(t23, negm_spec), e2, e3);
+      upk2(fadd2(pk2(t[i + 0], t[i + 1]), negm), e0, e1);
+      upk2(fadd2(pk2(t[i + 2], t[i + 3]), negm), e2, e3);
       const float p0 = CRAM_EX2_0(e0), p1 = CRAM_EX2_1(e1), p2 = CRAM_EX2_2(e2), p3 = CRAM_EX2_3(e3);
       la = fadd2(la, pk2(p0, p1));
       lb = fadd2(lb, pk2(p2, p3));
-      pk[c * 16 + i / 2 + 0] = pack2<T>(p0, p1);
-      pk[c * 16 + i / 2 + 1] = pack2<T>(p2, p3);
-#endif
+      pk[i / 2 + 0] = pack2<T>(p0, p1);
+      pk[i / 2 + 1] = pack2<T>(p2, p3);
     }
+    ptx::tmem_st16(s_addr + c * 16, pk);
   }
-  const float mxa = fmaxf(mx0, mx1), mxb = fmaxf(mx2, mx3);
-  const float mx = fmaxf(mxa, mxb);
-
-  // lazy rescale: move the reference max only when this tile beats it by more than 2^8
-  const bool need = mx > m_ref + kRescaleThreshold;
-  const float m_new = need ? mx : m_ref;
-#ifndef CRAM_NO_SPEC_SOFTMAX
-  const bool redo = __any_sync(0xffffffffu, need);
-#else
-  const bool redo = true;
-#endif
-  if (redo) {
-    if (!first && __any_sync(0xffffffffu, need)) {
-      const float f = need ? ex2(m_ref - m_new) : 1.0f;  // m_ref = -inf gives 0
-      ptx::mbar_wait(o_done_bar, o_done_parity);         // P V of the previous tile has landed in O
-      ptx::tc_fence_after();
-      const uint64_t f2 = pk2(f, f);
-#pragma unroll
-      for (int c = 0; c < DH / 32; ++c) {
-        uint32_t o[32];
-        ptx::tmem_ld32(o_addr + c * 32, o);
-        ptx::tc_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float a, b;
-          upk2(fmul2(pk2(__uint_as_float(o[i]), __uint_as_float(o[i + 1])), f2), a, b);
-          o[i] = __float_as_uint(a);
-          o[i + 1] = __float_as_uint(b);
-        }
-        ptx::tmem_st32(o_addr + c * 32, o);
-      }
-      l *= f;
-    }
-    m_ref = m_new;
-    const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
-    const uint64_t negm = pk2(-m_use, -m_use);
-    la = pk2(0.f, 0.f);
-    lb = pk2(0.f, 0.f);
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-#pragma unroll
-      for (int i = 0; i < 32; i += 4) {
-        float e0, e1, e2, e3;
-        upk2(fadd2(pk2(__uint_as_float(s[c][i + 0]), __uint_as_float(s[c][i + 1])), negm), e0, e1);
-        upk2(fadd2(pk2(__uint_as_float(s[c][i + 2]), __uint_as_float(s[c][i + 3])), negm), e2, e3);
-        const float p0 = CRAM_EX2_0(e0), p1 = CRAM_EX2_1(e1), p2 = CRAM_EX2_2(e2), p3 = CRAM_EX2_3(e3);
-        la = fadd2(la, pk2(p0, p1));
-        lb = fadd2(lb, pk2(p2, p3));
-        pk[c * 16 + i / 2 + 0] = pack2<T>(p0, p1);
-        pk[c * 16 + i / 2 + 1] = pack2<T>(p2, p3);
-      }
-    }
-  }
-  ptx::tmem_st32(s_addr, pk);  // P over the S columns: 64 keys -> 32 packed columns
   float l0, l1, l2, l3;
   upk2(la, l0, l1);
   upk2(lb, l2, l3);
-  l += (l0 + l1) + (l2 + l3);
+  return (l0 + l1) + (l2 + l3);
+}
+
+// O *= f, l *= f (f = 2^(m_old - m_new) per row): the correction step of the online softmax
+template <int DH>
+__device__ __forceinline__ void rescale_o(const uint32_t o_addr, const float f, float& l) {
+  const uint64_t f2 = pk2(f, f);
+#pragma unroll 1
+  for (int c = 0; c < DH / 32; ++c) {
+    uint32_t o[32];
+    ptx::tmem_ld32(o_addr + c * 32, o);
+    ptx::tc_wait_ld_regs(o);
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) {
+      float a, b;
+      upk2(fmul2(pk2(__uint_as_float(o[i]), __uint_as_float(o[i + 1])), f2), a, b);
+      o[i] = __float_as_uint(a);
+      o[i + 1] = __float_as_uint(b);
+    }
+    ptx::tmem_st32(o_addr + c * 32, o);
+  }
+  l *= f;
+}
+
+// One speculative pass over the 64 keys of half h (chunks 2h, 2h+1): P packed into pk, returns the row sum.
+// `between` runs after the first chunk (the main loop uses it to hand the previous half over to the MMA warp once its
+// tcgen05.st has had a chunk's worth of time to land).
+template <typename T, bool kDiag, typename Between>
+__device__ __forceinline__ float spec_half(const uint32_t s_addr, const uint32_t bias, const uint64_t sc2, const int climit,
+                                           const float m_ref, const int h, uint32_t (&pk)[32], Between&& between) {
+  const float m_spec = (m_ref == -INFINITY) ? 0.f : m_ref;
+  const uint64_t negm = pk2(-m_spec, -m_spec);
+  uint64_t la = pk2(0.f, 0.f), lb = pk2(0.f, 0.f);
+  uint32_t raw[2][32];
+  // TMEM -> registers in 32-column chunks; the load of the second chunk is in flight while the first is processed.
+  ptx::tmem_ld32(s_addr + (2 * h) * 32, raw[0]);
+#pragma unroll
+  for (int cc = 0; cc < 2; ++cc) {
+    ptx::tc_wait_ld_regs(raw[cc]);
+    if (cc == 0) ptx::tmem_ld32(s_addr + (2 * h + 1) * 32, raw[1]);
+    float t[32];
+    score_chunk<kDiag>(raw[cc], bias, 2 * h + cc, sc2, climit, t);
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      float e0, e1, e2, e3;
+      upk2(fadd2(pk2(t[i + 0], t[i + 1]), negm), e0, e1);
+      upk2(fadd2(pk2(t[i + 2], t[i + 3]), negm), e2, e3);
+      const float p0 = CRAM_EX2_0(e0), p1 = CRAM_EX2_1(e1), p2 = CRAM_EX2_2(e2), p3 = CRAM_EX2_3(e3);
+      la = fadd2(la, pk2(p0, p1));
+      lb = fadd2(lb, pk2(p2, p3));
+      pk[cc * 16 + i / 2 + 0] = pack2<T>(p0, p1);
+      pk[cc * 16 + i / 2 + 1] = pack2<T>(p2, p3);
+    }
+    if (cc == 0) between();
+  }
+  float l0, l1, l2, l3;
+  upk2(la, l0, l1);
+  upk2(lb, l2, l3);
+  return (l0 + l1) + (l2 + l3);
 }
 
 // ---- MMA issue helpers (compile-time K steps; see ptx::mma_ss_imm) ---------------------------------
@@ -315,10 +366,12 @@ __device__ __forceinline__ void issue_qk_steps(uint32_t d_tmem, uint32_t q_lo, u
 }
 // O += P V for key steps KK (16 keys each): P step kk sits at TMEM column offset 8*kk (packed 16-bit),
 // V step kk 16 rows x 128 B further down the MN-major tile.
-template <int... KK>
+template <int kFirst, int... KK>
 __device__ __forceinline__ void issue_pv_steps(uint32_t o_tmem, uint32_t p_tmem, uint32_t v_lo, uint32_t idesc,
                                                bool acc_first, std::integer_sequence<int, KK...>) {
-  (ptx::mma_ts_imm<kDescHi, 0, KK * 8, KK * 128>(o_tmem, p_tmem, v_lo, idesc, (acc_first || KK > 0) ? 1u : 0u), ...);
+  (ptx::mma_ts_imm<kDescHi, 0, (kFirst + KK) * 8, (kFirst + KK) * 128>(o_tmem, p_tmem, v_lo, idesc,
+                                                                       (acc_first || KK > 0) ? 1u : 0u),
+   ...);
 }
 
 template <typename T, int DH>
@@ -368,10 +421,10 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       ptx::mbar_init(&bar->q_full[i], 1);
       ptx::mbar_init(&bar->o_done[i], 1);
       ptx::mbar_init(&bar->o_final[i], 1);
-      for (int b = 0; b < 2; ++b) {
-        ptx::mbar_init(&bar->s_full[i][b], 1);
-        ptx::mbar_init(&bar->p_full[i][b], kBlockM);
-      }
+      ptx::mbar_init(&bar->s_full[i], 1);
+      ptx::mbar_init(&bar->p_full[i][0], kBlockM);
+      ptx::mbar_init(&bar->p_full[i][1], kBlockM);
+      ptx::mbar_init(&bar->o_half[i], 1);
     }
     for (int i = 0; i < kKV; ++i) {
       ptx::mbar_init(&bar->k_full[i], 1);
@@ -412,33 +465,28 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     setmaxnreg_dec<56>();
     if (warp == 8) {
       // ============================== producer ==================================================
-      // Order K[0], K[1], then per step t: K[t+2], V[t] -- Q K^T runs two tiles ahead of P V.
-      auto load_k_and_bias = [&](int j) {
-        const int st = j % kKV;
-        if (lane == 0 && j >= 2) {  // K[0], K[1] were issued before the CTA-wide sync
-          ptx::mbar_wait(&bar->k_empty[st], ((j / kKV) & 1) ^ 1);
-          ptx::mbar_expect_tx(&bar->k_full[st], S::kTileBytes);
-#pragma unroll
-          for (int sl = 0; sl < kSlabs; ++sl)
-            ptx::tma_load_2d(smem + S::kK + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_k, &bar->k_full[st],
-                             kv_head * DH + sl * 64, k0 + j * kBlockN);
-        }
-      };
-      if (n_max > 0) load_k_and_bias(0);
-      if (n_max > 1) load_k_and_bias(1);
+      // Order K[0], K[1] (before the CTA-wide sync), then per step j: V[j], K[j+2]. A slot is re-filled as soon as the
+      // last MMA that reads it has completed (k_empty / v_empty are tcgen05.commit arrivals).
       for (int j = 0; j < n_max; ++j) {
-        if (lane == 0) CRAM_TRACE(10, j, 0);
-        if (j + 2 < n_max) load_k_and_bias(j + 2);
-        const int st = j % kKV;
         if (lane == 0) {
-          CRAM_TRACE(10, j, 1);
+          const int st = j % kKV;
+          CRAM_TRACE(10, j, 0);
           ptx::mbar_wait(&bar->v_empty[st], ((j / kKV) & 1) ^ 1);
-          CRAM_TRACE(10, j, 2);
+          CRAM_TRACE(10, j, 1);
           ptx::mbar_expect_tx(&bar->v_full[st], S::kTileBytes);
 #pragma unroll
           for (int sl = 0; sl < kSlabs; ++sl)
             ptx::tma_load_2d(smem + S::kV + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_v, &bar->v_full[st],
                              kv_head * DH + sl * 64, k0 + j * kBlockN);
+          CRAM_TRACE(10, j, 2);
+          if (j + 2 < n_max) {
+            ptx::mbar_wait(&bar->k_empty[st], (((j + 2) / kKV) & 1) ^ 1);
+            ptx::mbar_expect_tx(&bar->k_full[st], S::kTileBytes);
+#pragma unroll
+            for (int sl = 0; sl < kSlabs; ++sl)
+              ptx::tma_load_2d(smem + S::kK + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_k, &bar->k_full[st],
+                               kv_head * DH + sl * 64, k0 + (j + 2) * kBlockN);
+          }
           CRAM_TRACE(10, j, 3);
         }
         __syncwarp();
@@ -446,33 +494,33 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     } else if (warp == 10) {
       // ============================== bias vectors ===============================================
       // Its own warp (on a different sub-partition than the TMA producer): the log-credibility loads are dependent
-      // global loads, and behind the TMA issue they kept the producer one tile ahead instead of four. The vector of
-      // tile j (already x log2e, -inf past the key length) lives in a ring of 8 until every P V[j] is done; tile j is
-      // written once the V slot of tile j-4 has been seen free (the producer's own condition for V[j], so the phase
-      // parity cannot alias: that barrier's next completion needs this very vector) -- four tiles of slack.
+      // global loads, and behind the TMA issue they kept the producer from running ahead. The vector of tile j
+      // (already x log2e, -inf past the key length) lives in a ring of 4 until every P V[j] is done; tile j is
+      // written once the V slot of tile j-2 has been seen free (the producer's own condition for V[j], so the phase
+      // parity cannot alias: that barrier's next completion needs this very vector) -- two tiles of slack.
       const bool biased = p.logcred != nullptr && ((p.head_mask >> head) & 1ull);
       const int bias_len = p.bias_len ? p.bias_len[seq] : len_k;
       for (int j = 0; j < n_max; ++j) {
         if (j >= kKV) ptx::mbar_wait(&bar->v_empty[j % kKV], ((j / kKV) & 1) ^ 1);
-        float2 b2;
-        float* bp = reinterpret_cast<float*>(&b2);
+        float4 b4;
+        float* bp = reinterpret_cast<float*>(&b4);
 #pragma unroll
-        for (int e = 0; e < 2; ++e) {
-          const int key = j * kBlockN + lane * 2 + e;
+        for (int e = 0; e < 4; ++e) {
+          const int key = j * kBlockN + lane * 4 + e;
           float v = 0.f;
           if (key >= len_k) v = -INFINITY;
           else if (biased && key < bias_len) v = load_logcred(p.logcred, (int64_t)k0 + key, p.logcred_dtype) * kLog2e;
           bp[e] = v;
         }
-        reinterpret_cast<float2*>(s_bias + (j % kBiasRing) * kBlockN)[lane] = b2;
+        reinterpret_cast<float4*>(s_bias + (j % kBiasRing) * kBlockN)[lane] = b4;
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&bar->bias_full[j % kBiasRing]);
       }
     } else if (warp == 9 && ptx::elect_one_sync()) {
       // ============================== MMA issuer ================================================
-      // Per query stage s the S accumulator is double-buffered (2 x 64 columns): Q K^T of tile j+2 goes
-      // into the buffer whose P (tile j) the P V just issued has consumed -- the tensor pipe executes in
-      // order -- so S of the next tile is always ready while the softmax warps work on the current one.
+      // Per query stage s the chain is Q K^T(j) -> softmax(j) -> P V(j) -> Q K^T(j+1): S is single-buffered and P
+      // aliases it, the tensor pipe executes in order, so Q K^T(j+1) issued behind P V(j) cannot overtake it. While
+      // stage s waits for its softmax, the pipe runs the other stage's P V + Q K^T (1024 cycles at d = 128).
       const uint32_t q_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + S::kQ), 16);
       const uint32_t k_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + S::kK), 16);
       const uint32_t v_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + S::kV), S::kSlabBytes);
@@ -482,20 +530,17 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         const int st = j % kKV;
         ptx::mbar_wait(&bar->k_full[st], (j / kKV) & 1);
         ptx::tc_fence_after();
-        issue_qk_steps(tmem_base + s * 128 + (j & 1) * kBlockN, q_lo + s * kQTile16, k_lo + st * kTile16, kIdescQK,
+        issue_qk_steps(tmem_base + s * 128, q_lo + s * kQTile16, k_lo + st * kTile16, kIdescQK,
                        std::make_integer_sequence<int, DH / 16>{});
-        ptx::tc_commit(&bar->s_full[s][j & 1]);
+        ptx::tc_commit(&bar->s_full[s]);
         if (s == 1 || j >= n_t1) ptx::tc_commit(&bar->k_empty[st]);  // last stage to read K[j]
       };
 #pragma unroll
       for (int s = 0; s < kStages; ++s)
-        if ((s ? n_t1 : n_t0) > 0) ptx::mbar_wait(&bar->q_full[s], 0);
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-#pragma unroll
-        for (int s = 0; s < kStages; ++s)
-          if (j < (s ? n_t1 : n_t0)) issue_qk(s, j);
-      }
+        if ((s ? n_t1 : n_t0) > 0) {
+          ptx::mbar_wait(&bar->q_full[s], 0);
+          issue_qk(s, 0);
+        }
       for (int j = 0; j < n_max; ++j) {
         const int st = j % kKV;
 #pragma unroll
@@ -505,15 +550,20 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
           CRAM_TRACE(8 + s, j, 0);
           ptx::mbar_wait(&bar->v_full[st], (j / kKV) & 1);
           CRAM_TRACE(8 + s, j, 1);
-          ptx::mbar_wait(&bar->p_full[s][j & 1], (j >> 1) & 1);
+          ptx::mbar_wait(&bar->p_full[s][0], j & 1);
+          ptx::tc_fence_after();
+          issue_pv_steps<0>(tmem_base + 256 + s * 128, tmem_base + s * 128, v_lo + st * kTile16, kIdescPV, j > 0,
+                            std::make_integer_sequence<int, kBlockN / 32>{});
+          ptx::tc_commit(&bar->o_half[s]);
+          ptx::mbar_wait(&bar->p_full[s][1], j & 1);
           ptx::tc_fence_after();
           CRAM_TRACE(8 + s, j, 2);
-          issue_pv_steps(tmem_base + 256 + s * 128, tmem_base + s * 128 + (j & 1) * kBlockN, v_lo + st * kTile16,
-                         kIdescPV, j > 0, std::make_integer_sequence<int, kBlockN / 16>{});
+          issue_pv_steps<kBlockN / 32>(tmem_base + 256 + s * 128, tmem_base + s * 128, v_lo + st * kTile16, kIdescPV, true,
+                                       std::make_integer_sequence<int, kBlockN / 32>{});
           ptx::tc_commit(&bar->o_done[s]);
           if (j == nt - 1) ptx::tc_commit(&bar->o_final[s]);
           if (s == 1 || j >= n_t1) ptx::tc_commit(&bar->v_empty[st]);  // last stage to read V[j]
-          if (j + 2 < nt) issue_qk(s, j + 2);
+          if (j + 1 < nt) issue_qk(s, j + 1);
           CRAM_TRACE(8 + s, j, 3);
         }
       }
@@ -531,28 +581,72 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     const float scale2 = p.scale * kLog2e;
     const uint32_t bias_addr = ptx::smem_u32(s_bias);
     const int nt = s ? n_t1 : n_t0;
-    float m_ref = -INFINITY, l = 0.f;
+    float m_ref = -INFINITY, m_next = -INFINITY, l = 0.f;
+    const uint64_t sc2 = pk2(scale2, scale2);
+
+    // hand a half of P over to the MMA warp: its tcgen05.st must have completed
+    auto release = [&](int h) {
+      ptx::tc_wait_st();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(&bar->p_full[s][h]);
+    };
 
     for (int j = 0; j < nt; ++j) {
       const int bs = j % kBiasRing;
       if (lane == 0) CRAM_TRACE(warp, j, 0);
       ptx::mbar_wait(&bar->bias_full[bs], (j / kBiasRing) & 1);
-      ptx::mbar_wait(&bar->s_full[s][j & 1], (j >> 1) & 1);
+      ptx::mbar_wait(&bar->s_full[s], j & 1);
       ptx::tc_fence_after();
       if (lane == 0) CRAM_TRACE(warp, j, 1);
       const bool diag_tile = p.causal && (j * kBlockN + kBlockN - 1 > mt * kBlockM + diag);
       const int climit = qrow + diag - j * kBlockN;  // columns <= climit are visible
-      const uint32_t s_addr = s_base + (j & 1) * kBlockN;
-      if (diag_tile)
-        softmax_tile<T, DH, true>(s_addr, o_addr, bias_addr + bs * kBlockN * 4, scale2, climit, j == 0, &bar->o_done[s],
-                                  (j - 1) & 1, m_ref, l);
-      else
-        softmax_tile<T, DH, false>(s_addr, o_addr, bias_addr + bs * kBlockN * 4, scale2, climit, j == 0,
-                                   &bar->o_done[s], (j - 1) & 1, m_ref, l);
-      if (lane == 0) CRAM_TRACE(warp, j, 2);
-      ptx::tc_wait_st();
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(&bar->p_full[s][j & 1]);
+      const uint32_t b_addr = bias_addr + bs * kBlockN * 4;
+
+      auto tile = [&](auto diag_tag) {
+        constexpr bool kDiag = decltype(diag_tag)::value;
+        if (j == 0) {
+          // reference of a fresh row block: the max of its first 32 keys (column 0 is visible to every row)
+          m_ref = chunks_max<kDiag>(s_base, b_addr, sc2, climit, 0, 1);
+          m_next = m_ref;
+        } else {
+          // delayed lazy rescale: a row whose previous tile asked for a larger reference moves now. s_full(j) has been
+          // observed and Q K^T(j) was issued behind P V(j-1), so O holds every product up to tile j-1.
+          const bool pend = m_next > m_ref;
+          if (__any_sync(0xffffffffu, pend)) {
+            rescale_o<DH>(o_addr, pend ? ex2(m_ref - m_next) : 1.0f, l);
+            m_ref = m_next;
+          }
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t pk[32];
+          const float sum = spec_half<T, kDiag>(s_base, b_addr, sc2, climit, m_ref, h, pk, [&] {
+            if (h == 1) release(0);  // P of the first half was stored one chunk ago
+          });
+          // a row with no reference yet (every key so far masked out or of zero credibility) that now sees one
+          const bool exact = !(sum < ExactAbove<T>::value) || (m_ref == -INFINITY && sum > 0.f);
+          if (__any_sync(0xffffffffu, exact)) {
+            // exact path (rare). O must hold every product issued so far before it is rescaled.
+            const float mx = chunks_max<kDiag>(s_base, b_addr, sc2, climit, 2 * h, 2 * h + 2);
+            const float m_new = exact ? fmaxf(mx, m_ref) : m_ref;
+            if (h == 1) {
+              ptx::mbar_wait(&bar->o_half[s], j & 1);
+              ptx::tc_fence_after();
+            }
+            if (j > 0 || h == 1) rescale_o<DH>(o_addr, (m_new > m_ref) ? ex2(m_ref - m_new) : 1.0f, l);
+            m_ref = m_new;
+            m_next = fmaxf(m_next, m_ref);
+            l += exact_pass<T, kDiag>(s_base, b_addr, sc2, climit, m_ref, 2 * h, 2 * h + 2);
+          } else {
+            ptx::tmem_st32(s_base + h * 32, pk);
+            l += sum;
+            if (!(sum < kSoftAbove)) m_next = fmaxf(m_next, m_ref + __log2f(sum));  // >= the true max of this half
+          }
+          if (h == 1) release(1);
+        }
+      };
+      if (diag_tile) tile(std::true_type{});
+      else tile(std::false_type{});
       if (lane == 0) CRAM_TRACE(warp, j, 3);
     }
 
@@ -684,5 +778,8 @@ int launch_attn_sm100(const cram_attn_prefill_params& p, cudaStream_t stream) {
 #ifdef CRAM_ATTN_TRACE
 extern "C" int cram_debug_read_trace(long long* host_out) {
   return cudaMemcpyFromSymbol(host_out, cram::g_trace, sizeof(cram::g_trace)) == cudaSuccess ? 0 : -1;
+}
+extern "C" int cram_debug_read_trace_fine(long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, cram::g_trace_fine, sizeof(cram::g_trace_fine)) == cudaSuccess ? 0 : -1;
 }
 #endif

@@ -54,6 +54,17 @@ def run():
             prev = e[0]
             print(f"  j={j:2d} start={e[0]-t0:7d}  {e[1]-e[0]:6d} {e[2]-e[1]:6d} {e[3]-e[2]:6d} | {per:6d}")
 
+    if hasattr(lib, "cram_debug_read_trace_fine"):
+        fine = np.zeros((16, 16), dtype=np.int64)
+        lib.cram_debug_read_trace_fine.argtypes = [ctypes.c_void_p]
+        lib.cram_debug_read_trace_fine(fine.ctypes.data)
+        print("--- fine stamps of warp 0 (tiles 16..31): deltas between consecutive stamps 0..12 "
+              "(0 entry | c0 data, c0 done | c1 data, c1 done | c2 .. | c3 .. | 9 decided | 10 P issued | 11 st waited | 12 arrived)")
+        for r in fine:
+            if r[0] == 0:
+                continue
+            print("  " + " ".join(f"{int(r[i + 1] - r[i]):5d}" for i in range(12)))
+
 if __name__ == "__main__":
     if sys.argv[1] == "build":      # build <block | -1 = no trace> [DEFINE=VAL ...] [out=path]
         outs = [a[4:] for a in sys.argv[3:] if a.startswith("out=")]
