@@ -36,7 +36,7 @@ def run():
         ops.attn_prefill(q, k, v, cu, T, H, Hkv, dh, logcred=lc, head_mask=0x0FFFFFFF, kernel=2)
     torch.cuda.synchronize()
     lib = _lib.load()
-    buf = np.zeros((12, 64, 4), dtype=np.int64)
+    buf = np.zeros((24, 64, 4), dtype=np.int64)
     lib.cram_debug_read_trace.argtypes = [ctypes.c_void_p]
     assert lib.cram_debug_read_trace(buf.ctypes.data) == 0
     t0 = buf[buf > 0].min()
