@@ -60,6 +60,22 @@ class SweepCapture:
     attn: List[torch.Tensor] = field(default_factory=list)   # clean attention output
 
 
+@dataclass
+class SuffixTail:
+    """The last n rows of each of n_seq packed sequences of length T (what the IE sweep reads, re_weighting.py:160)."""
+    n: int
+    rows: torch.Tensor        # int64 [n_seq * n] packed row indices
+    positions: torch.Tensor   # int32 [n_seq * n] position of those rows inside their sequence
+    cu_q: torch.Tensor        # int32 [n_seq + 1] = arange * n
+
+    @classmethod
+    def make(cls, n_seq: int, T: int, n: int, device) -> "SuffixTail":
+        base = torch.arange(n_seq, device=device, dtype=torch.int64)[:, None] * T
+        off = torch.arange(T - n, T, device=device, dtype=torch.int64)[None, :]
+        return cls(n, (base + off).reshape(-1), off.expand(n_seq, n).reshape(-1).to(torch.int32).contiguous(),
+                   torch.arange(n_seq + 1, device=device, dtype=torch.int32) * n)
+
+
 class PagedKV:
     """Paged KV cache: per layer K and V of shape [n_pages, page_size, n_kv_heads, head_dim]."""
 
@@ -229,12 +245,23 @@ class CramEngine:
         return x
 
     def suffix_from_attn(self, l: int, x: torch.Tensor, attn: torch.Tensor, cu_seqlens: torch.Tensor, max_seqlen: int,
-                         positions: torch.Tensor, attn_kernel: int = 0) -> torch.Tensor:
+                         positions: torch.Tensor, attn_kernel: int = 0, tail: Optional["SuffixTail"] = None) -> torch.Tensor:
         """Continue a forward from layer l's attention output (sweep: variants differ from here on).
-        x is the residual stream entering layer l's o_proj add; it is updated in place and returned."""
+        x is the residual stream entering layer l's o_proj add; it is updated in place and returned.
+
+        With ``tail`` (the sweep only reads the last n rows of every sequence) the LAST layer does only the work those
+        rows need -- exact, no approximation: K and V of every row, but Q, the attention, o_proj, the MLP and the
+        residual stream for the tail rows alone. Returns the final residual stream of the tail rows [n_seq * n, hidden]."""
         s = self.spec
+        last = s.num_layers - 1
+        if tail is not None and l == last:
+            xt = x.index_select(0, tail.rows)
+            xt.add_(self.layer_post(l, xt, attn.index_select(0, tail.rows)))
+            return xt
         pending = self.layer_post(l, x, attn)
         for j in range(l + 1, s.num_layers):
+            if tail is not None and j == last:
+                return self._last_layer_tail(j, x, pending, cu_seqlens, max_seqlen, positions, tail, attn_kernel)
             qkv = self._qkv(j, x, pending, positions)
             q, k, v = self.split_qkv(qkv)
             a = ops.attn_prefill(q, k, v, cu_seqlens, max_seqlen, s.num_heads, s.num_kv_heads, s.head_dim,
@@ -242,6 +269,25 @@ class CramEngine:
             pending = self.layer_post(j, x, a)
         x.add_(pending)
         return x
+
+    def _last_layer_tail(self, j: int, x: torch.Tensor, pending: torch.Tensor, cu_seqlens: torch.Tensor, max_seqlen: int,
+                         positions: torch.Tensor, tail: "SuffixTail", attn_kernel: int) -> torch.Tensor:
+        """Layer j for the tail rows only: K / V projections of every row (the tail queries attend to all of them), the Q
+        projection, attention (len_q = n < len_k = T, the kernel's chunked-prefill mode), o_proj and MLP of n rows."""
+        s = self.spec
+        qd = s.num_heads * s.head_dim
+        h = ops.rmsnorm(x, self.w[f"in_norm.{j}"], s.rms_eps, residual=pending)  # x += pending (in place)
+        w, b = self.w[f"wqkv.{j}"], self.w.get(f"bqkv.{j}")
+        kv = F.linear(h, w[qd:], None if b is None else b[qd:])
+        ops.rope_(kv, s.num_kv_heads, s.head_dim, self.cos, self.sin, positions)
+        q = F.linear(h.index_select(0, tail.rows), w[:qd], None if b is None else b[:qd])
+        ops.rope_(q, s.num_heads, s.head_dim, self.cos, self.sin, tail.positions)
+        kd = s.num_kv_heads * s.head_dim
+        a = ops.attn_prefill(q, kv[:, :kd], kv[:, kd:], tail.cu_q, tail.n, s.num_heads, s.num_kv_heads, s.head_dim,
+                             cu_seqlens_k=cu_seqlens, max_seqlen_k=max_seqlen, kernel=attn_kernel)
+        xt = x.index_select(0, tail.rows)
+        xt.add_(self.layer_post(j, xt, a))
+        return xt
 
     def logits(self, x_rows: torch.Tensor) -> torch.Tensor:
         """Final norm + lm_head on selected rows of the final residual stream."""

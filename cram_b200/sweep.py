@@ -30,32 +30,67 @@ def heads_of_rank(n_heads: int, rank: int, world_size: int) -> List[int]:
 def assemble_gathered(gathered: Sequence[torch.Tensor], n_layers: int, n_heads: int, world_size: int) -> torch.Tensor:
     """Inverse of the head partition: gathered[r] is rank r's [L, len(heads_of_rank(r))] slice (padded to the
     widest rank with NaN when H % N != 0)."""
-    out = torch.full((n_layers, n_heads), float("nan"), dtype=gathered[0].dtype, device=gathered[0].device)
+    lead = tuple(gathered[0].shape[:-2])  # () for one prompt, (P,) for a stack of prompts
+    out = torch.full(lead + (n_layers, n_heads), float("nan"), dtype=gathered[0].dtype, device=gathered[0].device)
     for r in range(world_size):
         hs = heads_of_rank(n_heads, r, world_size)
         if hs:
-            out[:, hs] = gathered[r][:, :len(hs)]
+            out[..., hs] = gathered[r][..., :len(hs)]
     return out
 
 
 class IESweep:
+    """Kernel (3) as a component: one object per engine, pre-allocated variant buffers, one entry per prompt
+    (``cal_ie``) or per list of prompts (``run``, one all_gather for all of them)."""
+
     def __init__(self, engine: CramEngine, rank: int = 0, world_size: int = 1, group=None,
-                 variant_chunk: int = 4, max_rows: int = 1 << 17, attn_kernel: int = 0):
+                 variant_chunk: int = 4, max_rows: int = 1 << 17, attn_kernel: int = 0, tail_only_last_layer: bool = True):
         """variant_chunk: how many single-head variants go through the suffix layers per batch. It is
         FIXED (not "all of this rank's heads") so every GEMM sees the same M whatever the rank count;
-        that is what makes the sharded sweep bit-identical to the unsharded one."""
+        that is what makes the sharded sweep bit-identical to the unsharded one.
+        tail_only_last_layer: exact work skipping -- the answer logits only read the last n rows, so the last layer of
+        every suffix projects Q, attends, and runs o_proj / MLP for those rows alone (engine.suffix_from_attn)."""
         self.engine = engine
         self.rank, self.world_size, self.group = rank, world_size, group
         self.variant_chunk = variant_chunk
         self.max_rows = max_rows
         self.attn_kernel = attn_kernel
+        self.tail_only = tail_only_last_layer
+        self.heads = heads_of_rank(engine.spec.num_heads, rank, world_size)
+        self._bufs = {}     # (T, n_var) -> dict of reusable device tensors
+        self._heads_t = {}  # n_var chunking of self.heads -> int32 device tensors (constant across prompts)
+        self.last_ori = None
+
+    # ---- reusable device state ------------------------------------------------------------------------
+    def _chunks(self, T: int):
+        per = max(1, min(self.variant_chunk, self.max_rows // T))
+        key = per
+        if key not in self._heads_t:
+            dev = self.engine.device
+            self._heads_t[key] = [(hs, torch.tensor(hs, dtype=torch.int32, device=dev))
+                                  for hs in (self.heads[c:c + per] for c in range(0, len(self.heads), per))]
+        return self._heads_t[key]
+
+    def _buffers(self, T: int, nv: int):
+        key = (T, nv)
+        if key not in self._bufs:
+            if len(self._bufs) > 8:   # prompts of many different lengths: keep the footprint bounded
+                self._bufs.clear()
+            eng, dev = self.engine, self.engine.device
+            self._bufs[key] = dict(
+                x=torch.empty(nv * T, eng.spec.hidden, dtype=eng.dtype, device=dev),
+                cu=torch.arange(nv + 1, dtype=torch.int32, device=dev) * T,
+                pos=torch.arange(T, dtype=torch.int32, device=dev).repeat(nv),
+                cu1=torch.tensor([0, T], dtype=torch.int32, device=dev),
+                tails={})
+        return self._bufs[key]
 
     @torch.no_grad()
     def clean_pass(self, input_ids: torch.Tensor, answer_ids: torch.Tensor):
         """One clean forward; returns (capture, ori) with ori the device scalar of re_weighting.py:160."""
         eng = self.engine
         T = input_ids.numel()
-        cu = torch.tensor([0, T], dtype=torch.int32, device=input_ids.device)
+        cu = self._buffers(T, 1)["cu1"]
         cap = SweepCapture()
         x = eng.prefill(input_ids, cu, T, capture=cap, attn_kernel=self.attn_kernel)
         n = answer_ids.numel()
@@ -65,30 +100,41 @@ class IESweep:
 
     @torch.no_grad()
     def sweep_layer(self, cap: SweepCapture, l: int, heads: Sequence[int], logcred: torch.Tensor,
-                    answer_ids: torch.Tensor, ori: torch.Tensor) -> torch.Tensor:
-        """IE of `heads` of layer l -> f32 [len(heads)] on the device."""
+                    answer_ids: torch.Tensor, ori: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """IE of `heads` of layer l -> f32 [len(heads)] on the device. No host-built tensors and no allocation of
+        variant buffers inside the loop: they are cached per (prompt length, chunk size)."""
         eng, s = self.engine, self.engine.spec
-        dev = logcred.device
         T = cap.x_in[l].shape[0]
         n = answer_ids.numel()
-        cu1 = torch.tensor([0, T], dtype=torch.int32, device=dev)
+        chunks = self._chunks(T) if list(heads) == self.heads else [
+            (list(heads[c:c + self.variant_chunk]), torch.tensor(list(heads[c:c + self.variant_chunk]), dtype=torch.int32,
+                                                                 device=logcred.device))
+            for c in range(0, len(heads), self.variant_chunk)]
         q, k, v = eng.split_qkv(cap.qkv[l])
+        cu1 = self._buffers(T, 1)["cu1"]
         biased = ops.attn_prefill(q, k, v, cu1, T, s.num_heads, s.num_kv_heads, s.head_dim, logcred=logcred,
                                   head_mask=ops.heads_to_mask(heads), kernel=self.attn_kernel)
-        out = torch.empty(len(heads), dtype=torch.float32, device=dev)
-        per_chunk = max(1, min(self.variant_chunk, self.max_rows // T))
-        for c0 in range(0, len(heads), per_chunk):
-            hs = list(heads[c0:c0 + per_chunk])
+        if out is None:
+            out = torch.empty(len(heads), dtype=torch.float32, device=logcred.device)
+        c0 = 0
+        for hs, hs_t in chunks:
             nv = len(hs)
-            hs_t = torch.tensor(hs, dtype=torch.int32, device=dev)
+            buf = self._buffers(T, nv)
             variants = ops.sweep_splice_heads(cap.attn[l], biased, hs_t, s.num_heads, s.head_dim)
-            x = cap.x_in[l].repeat(nv, 1)
-            cu = torch.arange(nv + 1, dtype=torch.int32, device=dev) * T
-            pos = torch.arange(T, dtype=torch.int32, device=dev).repeat(nv)
-            x = eng.suffix_from_attn(l, x, variants.view(nv * T, -1), cu, T, pos, attn_kernel=self.attn_kernel)
-            tail = x.view(nv, T, s.hidden)[:, T - n:].contiguous()
-            _, ie = ops.sweep_answer_ie(tail, eng.w["norm"], s.rms_eps, eng.w["lm_head"], answer_ids, ori)
+            x = buf["x"]
+            x.view(nv, T, s.hidden).copy_(cap.x_in[l])  # broadcast over the variants (the suffix updates x in place)
+            tail = None
+            if self.tail_only:
+                if n not in buf["tails"]:
+                    from .engine import SuffixTail
+                    buf["tails"][n] = SuffixTail.make(nv, T, n, x.device)
+                tail = buf["tails"][n]
+            y = eng.suffix_from_attn(l, x, variants.view(nv * T, -1), buf["cu"], T, buf["pos"], attn_kernel=self.attn_kernel,
+                                     tail=tail)
+            rows = y.view(nv, n, s.hidden) if tail is not None else y.view(nv, T, s.hidden)[:, T - n:].contiguous()
+            _, ie = ops.sweep_answer_ie(rows, eng.w["norm"], s.rms_eps, eng.w["lm_head"], answer_ids, ori)
             out[c0:c0 + nv] = ie
+            c0 += nv
         return out
 
     @torch.no_grad()
@@ -99,16 +145,16 @@ class IESweep:
         layers = list(range(s.num_layers)) if layers is None else list(layers)
         cap, ori = self.clean_pass(input_ids, answer_ids)
         self.last_ori = ori
-        mine = heads_of_rank(s.num_heads, self.rank, self.world_size)
+        mine = self.heads
         width = (s.num_heads + self.world_size - 1) // self.world_size
         local = torch.full((s.num_layers, width), float("nan"), dtype=torch.float32, device=input_ids.device)
         if mine:
             for l in layers:
-                local[l, :len(mine)] = self.sweep_layer(cap, l, mine, logcred, answer_ids, ori)
+                self.sweep_layer(cap, l, mine, logcred, answer_ids, ori, out=local[l, :len(mine)])
         return local
 
     def gather(self, local: torch.Tensor) -> torch.Tensor:
-        """The path's only collective: one all_gather of the per-rank IE slices -> [L, H] on every rank."""
+        """The path's only collective: one all_gather of the per-rank IE slices -> [..., L, H] on every rank."""
         s = self.engine.spec
         return gather_ie(local, s.num_layers, s.num_heads, self.world_size, self.group)
 
@@ -117,6 +163,14 @@ class IESweep:
                layers: Optional[Sequence[int]] = None) -> torch.Tensor:
         """IE matrix [L, H] (f32, device) for one prompt; rows of layers not in `layers` are NaN."""
         return self.gather(self.local_ie(input_ids, logcred, answer_ids, layers))
+
+    @torch.no_grad()
+    def run(self, prompts: Sequence, layers: Optional[Sequence[int]] = None) -> torch.Tensor:
+        """Sweep a list of prompts, each (input_ids, logcred, answer_ids) on the device -> IE [P, L, H] on every rank
+        with ONE all_gather of f32[P, L, ceil(H/N)] at the end (512 KB per rank for P = 1000 at N = 8).
+        Nothing is read back to the host between prompts, so the next prompt's launches queue behind the current one's."""
+        locals_ = [self.local_ie(ids, lc, ans, layers) for ids, lc, ans in prompts]
+        return self.gather(torch.stack(locals_))
 
 
 def gather_ie(local: torch.Tensor, n_layers: int, n_heads: int, world_size: int, group=None) -> torch.Tensor:

@@ -67,3 +67,39 @@ def test_sweep_bf16_vs_oracle_bf16():
     e_ours, e_ref = np.abs(got - truth).max(), np.abs(want - truth).max()
     print(f"[sweep bf16] ours-vs-fp32 {e_ours:.3e}  oracle-bf16-vs-fp32 {e_ref:.3e}")
     assert e_ours <= 2 * e_ref + 2e-2
+
+
+def test_tail_only_last_layer_is_exact_work_skipping():
+    """The last layer of every suffix run for the answer rows alone (K / V of all rows, Q / attention / o_proj / MLP of n
+    rows) gives the IE of the full-row suffix: fp32 to rounding noise, and still equal to the oracle's cal_logits."""
+    ospec, sd, eng, ids, cred, ans = _setup(torch.float32)
+    lc = ops.log_cred(cred.to(DEV), torch.float32)
+    full = IESweep(eng, tail_only_last_layer=False).cal_ie(ids.to(DEV), lc, ans.to(DEV)).cpu().numpy()
+    tail = IESweep(eng, tail_only_last_layer=True).cal_ie(ids.to(DEV), lc, ans.to(DEV)).cpu().numpy()
+    print("[sweep tail-only vs full rows] max_abs", np.abs(full - tail).max())
+    assert np.abs(full - tail).max() <= 2e-5
+    with torch.no_grad():
+        want = np.array(orc.cal_logits(sd, ospec, ids[None], torch.log(cred)[None].float(), ans))
+    assert np.abs(tail - want).max() <= 5e-4
+
+
+def test_run_many_prompts_equals_one_by_one_and_reuses_buffers():
+    """IESweep.run: several prompts of different lengths and answer lengths, one gather at the end == cal_ie per prompt,
+    bit for bit; sharded over 4 simulated ranks too."""
+    ospec, sd, eng, ids, cred, ans = _setup(torch.bfloat16, T=260)
+    g = torch.Generator().manual_seed(9)
+    prompts = []
+    for T, n in ((260, 4), (200, 3), (260, 6)):
+        i = torch.randint(3, 500, (T,), generator=g)
+        a = torch.randint(3, 500, (n,), generator=g)
+        i[-n:] = a
+        c = torch.ones(T, dtype=torch.float16)
+        c[5:60] = 0.0
+        prompts.append((i.to(DEV), ops.log_cred(c.to(DEV), torch.bfloat16), a.to(DEV)))
+    sw = IESweep(eng, variant_chunk=2)
+    many = sw.run(prompts)
+    assert many.shape == (3, ospec.num_layers, ospec.num_heads) and not torch.isnan(many).any()
+    for p, pr in enumerate(prompts):
+        assert torch.equal(many[p], IESweep(eng, variant_chunk=2).cal_ie(*pr))
+    parts = [torch.stack([IESweep(eng, rank=r, world_size=4, variant_chunk=2).local_ie(*pr) for pr in prompts]) for r in range(4)]
+    assert torch.equal(assemble_gathered(parts, ospec.num_layers, ospec.num_heads, 4), many)
