@@ -1,21 +1,24 @@
 #!/usr/bin/env python
-"""bench.py -- CrAM credibility-reweighted prefill (BASELINE.json configs[1]) on N B200s of one node,
-plus the 32x32-head IE sweep (configs[2]) as a sub-measurement.
+"""bench.py -- CrAM credibility-reweighted prefill (BASELINE.json configs[1]) on N B200s of one node, with the other
+configurations of BASELINE.json as sub-records of the same JSON line: the 32x32-head IE sweep (configs[2], the part that
+shards), greedy decode over the paged KV cache (configs[3]) and the 70B / 32k long-context prefill (configs[4], N = 1).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-One "step" = one pass of the hot path over one batch: span index (kernel 2) -> 32-layer Llama-3-8B-shape
-prefill with the credibility bias on the selected heads (kernel 1 inside every layer) -> next-token
-argmax. Synthetic NQ-shaped prompts (question + 5 docs, ~2048 tokens, batch 16 per GPU), random-init
-bf16 weights. Prefill does not shard: --gpus N runs N independent replicas ("weak").
-The sweep is the part that shards; its heads/s at this N is reported under "sweep".
+One "step" = one pass of the hot path over one batch: span index (kernel 2) -> 32-layer Llama-3-8B-shape prefill with the
+credibility bias on the selected heads (kernel 1 inside every layer) -> next-token argmax. Synthetic NQ-shaped prompts
+(question + 5 docs, ~2048 tokens, batch 16 per GPU), random-init bf16 weights. Prefill does not shard:
+--gpus N runs N independent replicas ("weak"). `value` = inputs resident in HBM; `e2e.value` = the same batch through the
+public API (Re_Weighting_Strategy.run_RAG_batch, from Python strings: prompt building, tokenisation, H2D, span index,
+prefill, D2H of the answer tokens, detokenisation), `e2e.from_pinned_ids` = the same from pre-tokenised pinned buffers.
 
---impl reference times the reference's own CPU path (the oracle port; the reference is Python and
-/root/reference does not travel to the GPU box) on the host cores for the same config.
+--impl reference times the reference's own CPU path (the oracle port; the reference is Python and /root/reference does
+not travel to the GPU box) on the host cores for the same config.
 """
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -32,8 +35,9 @@ import torch
 
 METRIC = "cram_reweighted_prefill_tokens_per_s"
 UNIT = "tokens/s"
-WORKLOAD = "llama3-8b-shape bf16 CrAM prefill, question+5 docs ~2048 tok, batch 16/GPU, top-894 heads"
 N_TOPK_HEADS = 894  # run.sh:4 of the reference (llama3, NQ)
+CPU_SAMPLE_LAYERS = 4
+T_START = time.time()
 
 
 def parse():
@@ -43,17 +47,20 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="prefill", choices=["prefill", "decode", "longctx"],
-                    help="prefill = BASELINE configs[1] (the default bench line); decode = configs[3] (Qwen2-7B shapes, paged "
-                         "KV, batch 64, 256 new tokens); longctx = configs[4] (Llama-3-70B shapes, 20 docs / 32k tokens)")
+                    help="prefill = BASELINE configs[1] (the default bench line, which carries sweep / decode / longctx as "
+                         "sub-records); decode / longctx = that configuration alone, as its own line")
     ap.add_argument("--batch", type=int, default=0, help="0 = the workload's own (16 prefill, 64 decode, 1 longctx)")
     ap.add_argument("--seq", type=int, default=0, help="0 = the workload's own (2048, 2048, 32768)")
     ap.add_argument("--docs", type=int, default=0, help="0 = the workload's own (5, 5, 20)")
     ap.add_argument("--new-tokens", type=int, default=256, help="decode workload: tokens generated per sequence per step")
     ap.add_argument("--page-size", type=int, default=16)
     ap.add_argument("--layers", type=int, default=0, help="debug only: fewer layers (marks the line invalid)")
-    ap.add_argument("--sweep-prompts", type=int, default=1, help="prompts for the IE-sweep sub-measurement (0 = skip)")
+    ap.add_argument("--sweep-prompts", type=int, default=2, help="prompts for the IE-sweep sub-measurement (0 = skip)")
     ap.add_argument("--sweep-layers", type=int, default=0, help="debug only: sweep only the last k layers")
+    ap.add_argument("--sub", default="auto", help="sub-records of the default line: auto (decode at every N, longctx at N = 1 "
+                                                  "while the run is younger than 4 min), none, or a comma list of decode,longctx")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-reference", action="store_true")
     ap.add_argument("--attn-kernel", type=int, default=0, help="0 auto (tcgen05), 1 generic, 2 tcgen05")
     a = ap.parse_args()
     dflt = {"prefill": (16, 2048, 5), "decode": (64, 2048, 5), "longctx": (1, 32768, 20)}[a.workload]
@@ -84,6 +91,19 @@ def make_prompts(tok, batch: int, seq: int, docs: int, seed0: int, sweep: bool =
             tok, seed0 + i, docs, seq - (8 if sweep else 0), lambda q_, p_: get_prompt(p_, q_), sweep_scores=sweep)
         qs.append(q); ps.append(paras); ss.append(scores); wr.append(wrong); lens.append(n)
     return qs, ps, ss, wr, lens
+
+
+def workload_config(args, world: int, n_layers: int, lens_rank0):
+    """The `config` object -- built by BOTH arms from the same arguments and the same (rank-0) prompts, so that the two
+    lines name the same configuration key for key."""
+    n_heads_biased = min(N_TOPK_HEADS, n_layers * 32)
+    return {"workload": f"llama3-8b-shape bf16 CrAM prefill, question+{args.docs} docs ~{args.seq} tok, batch {args.batch}/GPU, "
+                        f"top-{n_heads_biased} heads",
+            "batch_per_gpu": args.batch, "seq_len": args.seq, "docs": args.docs,
+            "tokens_per_step_per_gpu": int(sum(lens_rank0)), "layers": n_layers, "heads_biased": n_heads_biased,
+            "parallelism": f"replicas x{world} (prefill does not shard)",
+            "l2": "inputs larger than L2 (16 GB of weights streamed every step)",
+            "valid": args.layers == 0}
 
 
 class ClockSampler:
@@ -133,6 +153,19 @@ def measured_peaks():
     return 1590.0, 1400.0, 6650.0, "fallback"
 
 
+def ncu_traffic(kernel: str, shape: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` at `shape`, from the committed summary of an
+    `ncu --set full` capture (profiles/ncu_traffic.json, regenerated by scripts/ncu_traffic.py from the .ncu-rep of the
+    same commit). None when no capture of this kernel version / shape is committed -- never a literal."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(path):
+        return None
+    try:
+        return json.load(open(path)).get(kernel, {}).get(shape, {}).get("dram_bytes_per_launch")
+    except Exception:
+        return None
+
+
 # ---------------------------------------------------------------------------------------------------
 # CPU reference path (oracle port), used by --impl reference and by the cpu_baseline leg
 # ---------------------------------------------------------------------------------------------------
@@ -180,29 +213,36 @@ def cpu_reference_sample(seq: int, n_layers_sample: int, steps: int, warmup: int
     return tokens_per_s, ms, torch.get_num_threads()
 
 
+def cpu_sample_text(seq: int, batch: int, ms: float) -> str:
+    nl = CPU_SAMPLE_LAYERS
+    return (f"oracle port (the reference is Python; /root/reference does not travel): {nl} of 32 layers x 1 of {batch} sequences "
+            f"of {seq} tokens per step, hooked eager attention (28 heads per layer) + projections, bf16, {ms:.0f} ms per sample, "
+            f"extrapolated x{32 // nl}")
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
     # torchrun exports OMP_NUM_THREADS=1 to every rank; rank 0 alone works here, so give it the host's cores back
     # (the count an un-launched `python bench.py --impl reference` gets: physical cores).
-    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+    if world > 1:
         try:
             import psutil
             ncores = psutil.cpu_count(logical=False) or os.cpu_count()
         except ImportError:
             ncores = os.cpu_count()
         torch.set_num_threads(max(1, min(ncores or 1, len(os.sched_getaffinity(0)))))
-    nl = 2
-    tps, ms, cores = cpu_reference_sample(args.seq, nl, max(1, args.steps), max(0, args.warmup))
-    sample = (f"oracle port (reference is Python; /root/reference does not travel): {nl} of 32 layers x 1 of {args.batch} "
-              f"sequences of {args.seq} tokens per step, hooked eager attention + projections, bf16, extrapolated x{32 // nl}")
+    from cram_b200 import synth
+    tok = synth.load_tokenizer()
+    _, _, _, _, lens = make_prompts(tok, args.batch, args.seq, args.docs, seed0=0)
+    config = workload_config(args, world, 32 if not args.layers else args.layers, lens)
+    tps, ms, cores = cpu_reference_sample(args.seq, CPU_SAMPLE_LAYERS, max(1, args.steps), max(0, args.warmup))
     line = {"impl": "reference", "metric": METRIC, "value": tps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch_per_gpu": args.batch, "seq_len": args.seq, "docs": args.docs,
-                       "device": "host cpu"},
-            "cpu_baseline": {"value": tps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "dtype": "bf16", "data": "synthetic", "config": config, "device": "host cpu",
+            "cpu_baseline": {"value": tps, "unit": UNIT, "cores": cores, "kind": "port", "sample": cpu_sample_text(args.seq, args.batch, ms)},
             "e2e": {"value": tps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -267,12 +307,11 @@ def timed_steps(D: Dist, fn, steps: int, sampler=None) -> float:
 
 
 def run_ours(args):
-    from cram_b200 import ops, synth
+    from cram_b200 import _lib, ops, synth
     from cram_b200.engine import LLAMA3_8B, CramEngine, ModelSpec
-    from cram_b200.re_weighting import Find_Best_Heads, Re_Weighting_Strategy, _heads_dict_to_masks
+    from cram_b200.re_weighting import Re_Weighting_Strategy, _heads_dict_to_masks
 
     D = Dist()
-    dist = D.dist
     world, rank, local, dev = D.world, D.rank, D.local, D.dev
     barrier, allmax, allsum = D.barrier, D.allmax, D.allsum
 
@@ -290,8 +329,10 @@ def run_ours(args):
     lens = [len(x) for x in ids]
     total_tokens = int(sum(lens))
     max_len = int(max(lens))
+    lens_rank0 = lens if rank == 0 else None
+    config = workload_config(args, world, spec.num_layers, lens) if rank == 0 else None
 
-    # HOST buffers (pinned) of one batch: what the reference-facing call receives
+    # HOST buffers (pinned) of one batch: what a caller that tokenised beforehand holds
     pin = lambda a, dt: torch.from_numpy(np.ascontiguousarray(np.asarray(a, dtype=dt))).pin_memory()
     h = dict(ids=pin(np.concatenate(ids), np.int64), off=pin(np.concatenate(offs), np.int64), cu=pin(cu, np.int32),
              cud=pin(cud, np.int32), sb=pin(sb, np.int32), se=pin(se, np.int32), sc=pin(sc, np.float32))
@@ -305,12 +346,17 @@ def run_ours(args):
         x = engine.prefill(dd["ids"], dd["cu"], max_len, logcred=logcred, head_masks=masks, attn_kernel=args.attn_kernel)
         return engine.logits(x[last_rows]).argmax(-1)
 
-    def step_e2e():
+    def step_pinned():
         dd = {k: v.to(dev, non_blocking=True) for k, v in h.items()}
         nxt = step_device(dd)
         out_host.copy_(nxt, non_blocking=True)
         torch.cuda.current_stream().synchronize()  # the caller holds the answer tokens on the host
         return out_host
+
+    def step_api():
+        # the call a user of the reference makes, batched: strings in, strings out (utils/re_weighting.py:116-138 with
+        # max_new_tokens = 1: prompt building, tokenisation, offsets, H2D, span index, prefill, D2H, detokenisation)
+        return rw.run_RAG_batch(qs, ps, ss, max_new_tokens=1)
 
     with torch.no_grad():
         for _ in range(args.warmup):
@@ -336,18 +382,22 @@ def run_ours(args):
         all_tokens = allsum(float(total_tokens))
         value = all_tokens / (ms_step / 1e3)
 
-        # ---- timed: end to end from pinned host buffers -----------------------------------------------
-        step_e2e()
+        # ---- timed: end to end from pinned pre-tokenised host buffers -----------------------------------
+        step_pinned()
+        ms_pinned = timed_steps(D, step_pinned, args.steps)
+        # ---- timed: end to end through the public API, from strings (host wall clock: the tokeniser is host work) ----
+        step_api()
         barrier(); torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
+        t0 = time.perf_counter()
         for _ in range(args.steps):
-            step_e2e()
-        e1.record()
+            step_api()
         torch.cuda.synchronize()
+        ms_api = allmax((time.perf_counter() - t0) * 1e3 / args.steps)
         barrier()
-        ms_e2e = allmax(e0.elapsed_time(e1) / args.steps)
-        e2e_value = all_tokens / (ms_e2e / 1e3)
+        t0 = time.perf_counter()
+        rw._encode_batch(qs, ps, ss, [""] * args.batch)
+        ms_tokenise = (time.perf_counter() - t0) * 1e3
+        e2e_value = all_tokens / (ms_api / 1e3)
 
     # ---- roofline of the dominant OWN kernel: the tcgen05 attention launch ----------------------------
     peak, peak_sus, hbm, which = measured_peaks()
@@ -360,13 +410,12 @@ def run_ours(args):
     step_flops = 2.0 * p_layer * spec.num_layers * total_tokens + attn_flops * spec.num_layers + 2.0 * spec.vocab * spec.hidden * args.batch
     model_tflops = step_flops / (ms_step / 1e3) / 1e12
     # the launches are timed with events INSIDE the long step (SM clock under the power cap): the sustained figure is
-    # the denominator; the burst one (the kernel alone does 842-853 TFLOP/s, scripts/profile_attn.py) is kept beside it
+    # the denominator; the burst one (for the kernel timed alone, profiles/) is kept beside it
     roofline = {"bound": "tensor", "kernel": "attn_prefill_sm100_kernel<bf16,128>", "achieved": achieved, "peak": peak_sus,
                 "unit": "TFLOP/s", "frac": (achieved / peak_sus) if achieved else None,
                 "peak_burst": peak, "frac_of_burst": (achieved / peak) if achieved else None,
-                # dram__bytes_read.sum + dram__bytes_write.sum of one launch at this shape, ncu --set full
-                # (profiles/r1_attn_v4_ncu_and_trace.md); only recorded for the default shape
-                "traffic": 1.079e9 if (args.batch, args.seq, args.layers) == (16, 2048, 0) else None, "traffic_unit": "bytes/launch",
+                "traffic": ncu_traffic("attn_prefill_sm100", f"b{args.batch}_t{args.seq}") if not args.layers else None,
+                "traffic_unit": "bytes/launch",
                 "algorithmic_bytes": 2.0 * total_tokens * (2 * spec.num_heads + 2 * spec.num_kv_heads) * spec.head_dim,
                 "peak_source": f"{which} bf16_tflops_sustained (kernel timed inside the long step, between library GEMMs)",
                 "launch_ms": attn_avg_ms, "launches_timed": len(attn_ms),
@@ -377,74 +426,134 @@ def run_ours(args):
     # ---- CPU baseline (rank 0, N = 1 only) -------------------------------------------------------------
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        tps, ms_cpu, cores = cpu_reference_sample(args.seq, 2, 2, 1)
-        cpu_baseline = {"value": tps, "unit": UNIT, "cores": cores, "kind": "port",
-                        "sample": f"oracle port, 2 of 32 layers x 1 sequence of {args.seq} tokens (hooked eager, bf16), "
-                                  f"{ms_cpu:.0f} ms per sample, extrapolated x16"}
+        tps, ms_cpu, cores = cpu_reference_sample(args.seq, CPU_SAMPLE_LAYERS, 2, 1)
+        cpu_baseline = {"value": tps, "unit": UNIT, "cores": cores, "kind": "port", "sample": cpu_sample_text(args.seq, args.batch, ms_cpu)}
 
-    # ---- the reference's hooked eager attention executed by PyTorch on THIS GPU (context: the bar a user of the
-    # reference sees on a B200). One layer, one sequence: dense [1,H,T,T] mask rewrite
-    # (utils/re_weighting.py:36-61) + HF eager attention (modeling_llama.py:199-221), via the oracle's restatement.
+    # ---- the reference's own hooked HF path on THIS GPU (context: what a CrAM user's code achieves on a B200) ----------
     ref_on_gpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        try:
-            from oracle import cram_oracle as orc
-            T0 = int(lens[0])
-            gq = torch.randn(1, spec.num_heads, T0, spec.head_dim, device=dev).bfloat16()
-            gk = torch.randn(1, spec.num_kv_heads, T0, spec.head_dim, device=dev).bfloat16()
-            gv = torch.randn_like(gk)
-            base = torch.triu(torch.full((T0, T0), torch.finfo(torch.bfloat16).min, dtype=torch.bfloat16, device=dev), 1)[None, None]
-            lcg = torch.zeros(1, T0, dtype=torch.bfloat16, device=dev)
-            lcg[:, 16:T0 - 32] = -0.6931
-            hooked = list(range(28))
-
-            def ref_layer():
-                m = orc.edit_attention_mask(base, lcg, hooked, spec.num_heads, T0, T0, torch.bfloat16)
-                return orc.eager_attention(gq, gk, gv, m, spec.head_dim ** -0.5)
-
-            with torch.no_grad():
-                ref_layer(); torch.cuda.synchronize()
-                r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                r0.record()
-                for _ in range(3):
-                    ref_layer()
-                r1.record(); torch.cuda.synchronize()
-            ref_ms = r0.elapsed_time(r1) / 3
-            ref_on_gpu = {"what": "reference hook + HF eager attention through PyTorch on this GPU, one layer x one sequence (28 heads hooked)",
-                          "ms_per_layer_per_sequence": ref_ms, "ours_ms_per_layer_per_sequence": attn_avg_ms / args.batch,
-                          "ratio": ref_ms / (attn_avg_ms / args.batch) if attn_ms else None}
-        except Exception as e:  # context only: never fail the bench line on it
-            ref_on_gpu = {"error": repr(e)[:200]}
+    if rank == 0 and world == 1 and not args.no_gpu_reference:
+        ref_on_gpu = reference_on_this_gpu(engine, heads, d, lens, tok, dev, value / world, args)
 
     # ---- IE sweep sub-measurement (the part that shards) ------------------------------------------------
     sweep = None
     if args.sweep_prompts > 0:
         sweep = run_sweep(args, engine, tok, rank, world, dev, barrier, allmax, peak)
 
+    # ---- the other configurations of BASELINE.json as sub-records ------------------------------------------
+    del rw, d
+    engine = None
+    torch.cuda.empty_cache()
+    subs = {}
+    want = {"auto": ["decode", "longctx"], "none": []}.get(args.sub, [x for x in args.sub.split(",") if x])
+    for name in want:
+        if name == "longctx" and (world > 1 or (args.sub == "auto" and time.time() - T_START > 240)):
+            subs[name] = {"skipped": "N > 1" if world > 1 else "run older than 4 min; `python bench.py --workload longctx` runs it alone"}
+            continue
+        try:
+            subs[name] = run_sub(name, args, D)
+        except Exception as e:  # a sub-record must never cost the main line
+            subs[name] = {"error": repr(e)[:300]}
+        torch.cuda.empty_cache()
+
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
-                "data": "synthetic",
-                "config": {"workload": WORKLOAD, "batch_per_gpu": args.batch, "seq_len": args.seq, "docs": args.docs,
-                           "tokens_per_step_per_gpu": total_tokens, "layers": spec.num_layers, "heads_biased": sum(len(v) for v in heads.values()),
-                           "parallelism": f"replicas x{world} (prefill does not shard)",
-                           "l2": "inputs larger than L2 (16 GB of weights streamed every step)",
-                           "valid": args.layers == 0},
+                "data": "synthetic", "config": config,
                 "clocks": clocks.summary(),
-                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d_bytes,
-                        "d2h_bytes_per_step": int(out_host.numel() * out_host.element_size())},
+                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_api,
+                        "path": "Re_Weighting_Strategy.run_RAG_batch(questions, paras, scores, max_new_tokens=1): strings -> prompt "
+                                "+ tokeniser + offsets (host) -> pinned H2D -> span index -> prefill -> D2H tokens -> detokenise",
+                        "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": int(out_host.numel() * out_host.element_size()),
+                        "host_tokenise_ms": ms_tokenise,
+                        "from_pinned_ids": {"value": all_tokens / (ms_pinned / 1e3), "ms_per_step": ms_pinned,
+                                            "path": "pre-tokenised pinned buffers -> H2D -> span index -> prefill -> D2H"}},
                 "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu_baseline,
-                "reference_attention_on_this_gpu": ref_on_gpu, "sweep": sweep}
+                "reference_on_this_gpu": ref_on_gpu, "sweep": sweep, "decode": subs.get("decode"), "longctx": subs.get("longctx"),
+                "library": {"path": os.path.relpath(_lib.library_path(), ROOT), "fingerprint": _lib.library_fingerprint()[:16]},
+                "wall_s": round(time.time() - T_START, 1)}
         print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    D.close()
+
+
+def run_sub(name: str, args, D):
+    """decode (configs[3]) / longctx (configs[4]) as a compact sub-record of the default line."""
+    import copy
+    from bench_workloads import run_decode, run_longctx
+    a = copy.copy(args)
+    a.workload = name
+    a.batch, a.seq, a.docs = {"decode": (64, 2048, 5), "longctx": (1, 32768, 20)}[name]
+    a.steps, a.warmup = (2, 1) if name == "decode" else (2, 1)
+    a.no_cpu_baseline = True
+    full = (run_decode if name == "decode" else run_longctx)(a, D)
+    if full is None:
+        return None
+    r = full["roofline"]
+    out = {"metric": full["metric"], "value": full["value"], "unit": full["unit"], "ms_per_step": full["ms_per_step"],
+           "steps": a.steps, "warmup": a.warmup, "config": full["config"], "clocks": full["clocks"],
+           "e2e": {k: full["e2e"][k] for k in ("value", "ms_per_step", "h2d_bytes_per_step", "d2h_bytes_per_step")},
+           "gpu_launches": full["gpu_launches"],
+           "roofline": {k: r.get(k) for k in ("bound", "kernel", "achieved", "peak", "unit", "frac", "traffic", "launch_ms",
+                                              "launches_timed", "attn_share_of_step")},
+           "model_level": r.get("model_level")}
+    if name == "decode" and r.get("decode_mlp"):
+        m = r["decode_mlp"]
+        out["decode_mlp"] = {k: m.get(k) for k in ("kernel", "achieved", "peak", "frac", "unit", "ms_per_layer", "share_of_step")}
+    return out
+
+
+def reference_on_this_gpu(engine, heads, d, lens, tok, dev, ours_tok_s_per_gpu, args):
+    """The reference's hooked path (HF LlamaForCausalLM + forward_pre_hook rewriting the dense mask, utils/re_weighting.py:
+    36-61,120-124,159-174) run through PyTorch on this B200 -- via oracle/hf_hooked.py, a restatement pinned against the
+    unmodified reference on CPU (/root/reference does not travel). Same weights as the engine (aliased, no copy), b = 1 as
+    the reference runs it. Not an arm: context for the headline ratio."""
+    try:
+        from oracle import hf_hooked
+        T0 = int(lens[0])
+        ids0 = d["ids"][:T0]
+        # the reference hands torch.log(fp16 credibility) to the hook; any k/10-valued vector of the prompt's length does
+        lc = torch.zeros(T0, dtype=torch.float16, device=dev)
+        per = (T0 - 48) // 5
+        for j, sc in enumerate((0.0, 0.3, 0.5, 0.8, 1.0)):
+            lc[16 + j * per:16 + (j + 1) * per] = float(np.log(np.float16(sc))) if sc > 0 else float("-inf")
+        out = {"what": "oracle/hf_hooked.py: HF LlamaForCausalLM (engine's weights) + the reference's mask-rewriting hook, b = 1, "
+                       f"T = {T0}, bf16, {sum(len(v) for v in heads.values())} hooked heads", "kind": "port"}
+        for attn in ("eager", "sdpa"):
+            model = hf_hooked.hf_from_engine(engine, attn=attn)
+            with torch.no_grad():
+                run = lambda: hf_hooked.hooked_logits(model, ids0, lc, heads)[0, -1].argmax()
+                run(); torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(3):
+                    run()
+                e1.record(); torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1) / 3
+            out[f"prefill_tok_s_{attn}"] = T0 / (ms / 1e3)
+            out[f"prefill_ms_{attn}"] = ms
+            if attn == "eager":
+                # Find_Best_Heads.cal_logits: 1 clean + 1 full forward per head; 8 heads timed, heads/s extrapolates linearly
+                ans = ids0[-5:].clone()
+                pairs = [(l, h) for l in (0, engine.spec.num_layers - 1) for h in (0, 9, 17, 30)]
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                hf_hooked.cal_logits_heads(model, ids0, lc, ans.cpu(), pairs)
+                torch.cuda.synchronize()
+                s = time.perf_counter() - t0
+                out["sweep_heads_s"] = len(pairs) / s
+                out["sweep_sample"] = f"cal_logits over {len(pairs)} (layer, head) pairs + the clean forward: {s:.2f} s; the full 32x32 sweep is 128x that"
+            del model
+            torch.cuda.empty_cache()
+        out["ours_over_reference_prefill"] = ours_tok_s_per_gpu / max(out["prefill_tok_s_eager"], out["prefill_tok_s_sdpa"])
+        return out
+    except Exception as e:  # context only: never fail the bench line on it
+        return {"error": repr(e)[:300]}
 
 
 def run_sweep(args, engine, tok, rank, world, dev, barrier, allmax, peak):
-    """Find_Best_Heads.cal_logits over all L x H heads of `sweep_prompts` prompts, heads sharded over ranks."""
+    """Find_Best_Heads over all L x H heads of `sweep_prompts` prompts, heads sharded over ranks (IESweep.run: every prompt's
+    launches queue back to back, ONE all_gather of f32[P, L, H/N] at the end)."""
     from cram_b200 import ops
     from cram_b200.re_weighting import Find_Best_Heads
-    import torch.distributed as dist
     spec = engine.spec
     fb = Find_Best_Heads("llama3-8b-shape-random-init", tokenizer=tok, engine=engine, rank=rank, world_size=world)
     qs, ps, ss, wr, lens = make_prompts(tok, args.sweep_prompts, args.seq, args.docs, seed0=77, sweep=True)
@@ -459,30 +568,40 @@ def run_sweep(args, engine, tok, rank, world, dev, barrier, allmax, peak):
     with torch.no_grad():
         fb.sweep.cal_ie(*prepared[0], layers=[spec.num_layers - 1])  # warm-up: one cheap layer + the collective
         barrier(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for ids, lc, ans in prepared:
-            ie = fb.sweep.cal_ie(ids, lc, ans, layers=layers)
+        ie = fb.sweep.run(prepared, layers=layers)
         ie_host = ie.cpu()
         e1.record()
         torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
         barrier()
     ms = allmax(e0.elapsed_time(e1))
     n_heads_swept = len(layers) * spec.num_heads * len(prepared)
-    T = int(prepared[0][0].numel())
-    # minimal-necessary FLOPs with clean-prefix reuse, per prompt
+    # minimal-necessary FLOPs with clean-prefix reuse, per prompt. F is kept as defined there: the exact
+    # tail-only last layer (IESweep) does less than F, which shows as heads/s, not as a smaller F.
     H, dh, hid, mlp, L = spec.num_heads, spec.head_dim, spec.hidden, spec.intermediate, spec.num_layers
     p_layer = hid * (H * dh + 2 * spec.num_kv_heads * dh) + H * dh * hid + 3 * hid * mlp
-    f_layer = 2.0 * p_layer * T + 4.0 * T * T * dh * H / 2
-    f_1head = 4.0 * T * T * dh / 2 + 2.0 * T * H * dh * hid + 2.0 * T * 3 * hid * mlp
-    flops = sum(H * (f_1head + (L - 1 - l) * f_layer) for l in layers) * len(prepared)
+    flops = 0.0
+    for ids, _, _ in prepared:
+        T = int(ids.numel())
+        f_layer = 2.0 * p_layer * T + 4.0 * T * T * dh * H / 2
+        f_1head = 4.0 * T * T * dh / 2 + 2.0 * T * H * dh * hid + 2.0 * T * 3 * hid * mlp
+        flops += sum(H * (f_1head + (L - 1 - l) * f_layer) for l in layers)
     tf = flops / (ms / 1e3) / 1e12
+    sel = ie_host[:, layers]
+    per_prompt_s = ms / 1e3 / len(prepared)
     return {"metric": "ie_sweep_heads_per_s", "value": n_heads_swept / (ms / 1e3), "unit": "heads/s", "n_gpus": world,
-            "scaling": "strong", "prompts": len(prepared), "prompt_tokens": T, "layers_swept": len(layers),
-            "heads_per_layer": spec.num_heads, "ms": ms, "finite": bool(torch.isfinite(ie_host[layers]).all()),
+            "scaling": "strong", "prompts": len(prepared), "prompt_tokens": [int(p[0].numel()) for p in prepared],
+            "layers_swept": len(layers), "heads_per_layer": spec.num_heads, "ms": ms, "wall_s": wall,
+            "seconds_per_prompt": per_prompt_s, "projected_1000_prompts_s": 1000 * per_prompt_s,
+            "finite": bool(torch.isfinite(sel).all()),
+            # sha256 of the gathered fp32 IE matrices: equal across --gpus 1/2/4/8 = sharded == unsharded bit for bit
+            "ie_sha256": hashlib.sha256(sel.contiguous().numpy().tobytes()).hexdigest(),
             "roofline": {"bound": "tensor", "achieved": tf, "peak": peak * world, "unit": "TFLOP/s", "frac": tf / (peak * world),
                          "note": "F of SURVEY.md 8(d) (clean-prefix reuse) / wall / (N x burst bf16 peak)"},
-            "collective": "one all_gather of f32[L*H/N] per prompt" if world > 1 else "none (1 rank)",
+            "collective": "one all_gather of f32[P, L, H/N] for all prompts" if world > 1 else "none (1 rank)",
             "valid": args.sweep_layers == 0 and args.layers == 0}
 
 

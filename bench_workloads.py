@@ -13,7 +13,7 @@ import time
 import numpy as np
 import torch
 
-from bench import (ClockSampler, Dist, make_prompts, measured_peaks, seeded_head_set, timed_steps)
+from bench import (ClockSampler, Dist, make_prompts, measured_peaks, ncu_traffic, seeded_head_set, timed_steps)
 
 
 def _pin(a, dt):
@@ -112,12 +112,14 @@ def cpu_longctx_sample(spec, seq_sample: int = 2048, steps: int = 2, warmup: int
 # ---------------------------------------------------------------------------------------------------
 # configs[3]: greedy decode with the credibility bias over the paged KV cache
 # ---------------------------------------------------------------------------------------------------
-def run_decode(args):
+def run_decode(args, D=None):
+    """Standalone (D is None): prints the JSON line. As a sub-measurement of the default bench: returns it."""
     from cram_b200 import ops, synth
     from cram_b200.engine import QWEN2_7B, CramEngine, DecodeSession, ModelSpec, PagedKV
     from cram_b200.re_weighting import Re_Weighting_Strategy, _heads_dict_to_masks
 
-    D = Dist()
+    standalone = D is None
+    D = D or Dist()
     dev, rank, world = D.dev, D.rank, D.world
     spec = QWEN2_7B
     if args.layers:
@@ -266,8 +268,8 @@ def run_decode(args):
     model_gbs = (w_bytes + kv_step_bytes) / (ms_token_step / 1e3) / 1e9
     roofline = {"bound": "hbm", "kernel": "attn_decode_mma_kernel<bf16,128> (+combine when split)", "achieved": achieved,
                 "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                # dram read + write bytes of one launch at this shape from ncu --set full (profiles/r1_decode_ncu_summary.md)
-                "traffic": 290.1e6 if (B, args.seq, ps, args.layers) == (64, 2048, 16, 0) else None, "traffic_unit": "bytes/launch",
+                "traffic": ncu_traffic("attn_decode_mma", f"b{B}_t{args.seq}_p{ps}") if not args.layers else None,
+                "traffic_unit": "bytes/launch",
                 "peak_source": f"{which} hbm_gbs (copy bandwidth)", "launch_ms": dec_avg_ms, "launches_timed": reps * spec.num_layers,
                 "bytes_per_launch": kv_bytes,
                 "timing": "CUDA events around replays of a graph holding the step's attention launches (all layers, real caches)",
@@ -298,19 +300,28 @@ def run_decode(args):
                         "d2h_bytes_per_step": int(out_host.numel() * out_host.element_size()), "tokens_equal_device_run": same,
                         "includes": "H2D, span index, re-weighted prefill into the paged cache, decode, D2H of the tokens"},
                 "gpu_launches": launches_per_decode_step * new * args.steps, "roofline": roofline, "cpu_baseline": cpu_baseline}
-        print(json.dumps(line), flush=True)
-    D.close()
+        if standalone:
+            print(json.dumps(line), flush=True)
+    else:
+        line = None
+    del sess, kv, engine
+    torch.cuda.empty_cache()
+    if standalone:
+        D.close()
+    return line
 
 
 # ---------------------------------------------------------------------------------------------------
 # configs[4]: long-context prefill, Llama-3-70B shapes, 20 docs / 32k tokens
 # ---------------------------------------------------------------------------------------------------
-def run_longctx(args):
+def run_longctx(args, D=None):
+    """Standalone (D is None): prints the JSON line. As a sub-measurement of the default bench: returns it."""
     from cram_b200 import ops, synth
     from cram_b200.engine import LLAMA3_70B, CramEngine, ModelSpec
     from cram_b200.re_weighting import Re_Weighting_Strategy, _heads_dict_to_masks
 
-    D = Dist()
+    standalone = D is None
+    D = D or Dist()
     dev, rank, world = D.dev, D.rank, D.world
     spec = LLAMA3_70B
     if args.layers:
@@ -386,5 +397,12 @@ def run_longctx(args):
                 "e2e": {"value": all_tokens / (ms_e2e / 1e3), "unit": "tokens/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d_bytes,
                         "d2h_bytes_per_step": int(out_host.numel() * out_host.element_size())},
                 "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu_baseline}
-        print(json.dumps(line), flush=True)
-    D.close()
+        if standalone:
+            print(json.dumps(line), flush=True)
+    else:
+        line = None
+    del engine, rw
+    torch.cuda.empty_cache()
+    if standalone:
+        D.close()
+    return line
