@@ -442,8 +442,8 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       ptx::mbar_expect_tx(&bar->q_full[s], S::kQTileBytes);
 #pragma unroll
       for (int sl = 0; sl < kSlabs; ++sl)
-        ptx::tma_load_2d(smem + S::kQ + s * S::kQTileBytes + sl * S::kQSlabBytes, &tmap_q, &bar->q_full[s],
-                         head * DH + sl * 64, q0 + (pair * kStages + s) * kBlockM);
+        ptx::tma_load_2d_hint(smem + S::kQ + s * S::kQTileBytes + sl * S::kQSlabBytes, &tmap_q, &bar->q_full[s],
+                              head * DH + sl * 64, q0 + (pair * kStages + s) * kBlockM, ptx::kL2EvictFirst);
     }
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
@@ -451,8 +451,8 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       ptx::mbar_expect_tx(&bar->k_full[j], S::kTileBytes);
 #pragma unroll
       for (int sl = 0; sl < kSlabs; ++sl)
-        ptx::tma_load_2d(smem + S::kK + j * S::kTileBytes + sl * S::kSlabBytes, &tmap_k, &bar->k_full[j],
-                         kv_head * DH + sl * 64, k0 + j * kBlockN);
+        ptx::tma_load_2d_hint(smem + S::kK + j * S::kTileBytes + sl * S::kSlabBytes, &tmap_k, &bar->k_full[j],
+                              kv_head * DH + sl * 64, k0 + j * kBlockN, ptx::kL2EvictLast);
     }
   }
   if (warp == 9) ptx::tmem_alloc(tmem_ptr_smem, kTmemCols);
@@ -476,16 +476,16 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
           ptx::mbar_expect_tx(&bar->v_full[st], S::kTileBytes);
 #pragma unroll
           for (int sl = 0; sl < kSlabs; ++sl)
-            ptx::tma_load_2d(smem + S::kV + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_v, &bar->v_full[st],
-                             kv_head * DH + sl * 64, k0 + j * kBlockN);
+            ptx::tma_load_2d_hint(smem + S::kV + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_v, &bar->v_full[st],
+                                  kv_head * DH + sl * 64, k0 + j * kBlockN, ptx::kL2EvictLast);
           CRAM_TRACE(10, j, 2);
           if (j + 2 < n_max) {
             ptx::mbar_wait(&bar->k_empty[st], (((j + 2) / kKV) & 1) ^ 1);
             ptx::mbar_expect_tx(&bar->k_full[st], S::kTileBytes);
 #pragma unroll
             for (int sl = 0; sl < kSlabs; ++sl)
-              ptx::tma_load_2d(smem + S::kK + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_k, &bar->k_full[st],
-                               kv_head * DH + sl * 64, k0 + (j + 2) * kBlockN);
+              ptx::tma_load_2d_hint(smem + S::kK + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_k, &bar->k_full[st],
+                                    kv_head * DH + sl * 64, k0 + (j + 2) * kBlockN, ptx::kL2EvictLast);
           }
           CRAM_TRACE(10, j, 3);
         }
@@ -670,7 +670,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             v.y = pack2<T>(__uint_as_float(o[i + 2]) * inv, __uint_as_float(o[i + 3]) * inv);
             v.z = pack2<T>(__uint_as_float(o[i + 4]) * inv, __uint_as_float(o[i + 5]) * inv);
             v.w = pack2<T>(__uint_as_float(o[i + 6]) * inv, __uint_as_float(o[i + 7]) * inv);
-            *reinterpret_cast<uint4*>(out + c * 32 + i) = v;
+            __stcs(reinterpret_cast<uint4*>(out + c * 32 + i), v);  // written once, read by the next kernel: do not displace K / V in L2
           }
         }
       }

@@ -76,6 +76,18 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
       : "memory");
 }
 
+// L2 eviction-priority descriptors (createpolicy.fractional, fraction 1.0): what the cache-hint operand of a TMA load takes
+constexpr uint64_t kL2EvictFirst = 0x12F0000000000000ull;   // streamed once (Q tiles)
+constexpr uint64_t kL2EvictLast = 0x14F0000000000000ull;    // re-read by other CTAs (K / V tiles)
+__device__ __forceinline__ void tma_load_2d_hint(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
+                                                 uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+
 // one lane of the (converged) warp; ptxas treats code under this predicate as single-lane, so operands of
 // tcgen05.mma / commit become plain uniform registers instead of a waterfall loop
 __device__ __forceinline__ bool elect_one_sync() {

@@ -132,10 +132,12 @@ class Re_Weighting_Strategy:
             prompts.append(pr)
             flags.append(f)
         ids, offs, sb, se, sc, cu, cud = [], [], [], [], [], [0], [0]
-        for pr, f, ps, ss in zip(prompts, flags, paras_list, scores_list):
-            enc = self.tokenizer([pr], return_offsets_mapping=True, add_special_tokens=f)
-            ids.append(np.asarray(enc["input_ids"][0], dtype=np.int64))
-            offs.append(np.asarray([o[0] for o in enc["offset_mapping"][0]], dtype=np.int64))
+        # one tokenizer call for the whole batch (the fast tokenizer encodes the prompts in parallel); no padding, so
+        # every prompt gets exactly the ids / offsets of the reference's b = 1 call (:98)
+        enc_all = self.tokenizer(prompts, return_offsets_mapping=True, add_special_tokens=flags[0]) if prompts else None
+        for b, (pr, f, ps, ss) in enumerate(zip(prompts, flags, paras_list, scores_list)):
+            ids.append(np.asarray(enc_all["input_ids"][b], dtype=np.int64))
+            offs.append(np.asarray(enc_all["offset_mapping"][b], dtype=np.int64).reshape(-1, 2)[:, 0].copy())
             cu.append(cu[-1] + len(ids[-1]))
             for i, p in enumerate(ps):
                 para = ("Passage-%d: " % i) + p + "\n"

@@ -130,3 +130,26 @@ def test_splice_and_answer_ie():
             assert abs(cur[v].item() - float(want)) <= tol, (dtype, v, cur[v].item(), float(want))
         assert ie[0].item() == 0.0
         assert torch.allclose(ie, (cur0 - cur).to(dtype).float(), atol=1e-6)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_silu_mul_table_path_is_bit_identical_to_the_formula(dtype):
+    """Large inputs of a 16-bit dtype go through the 65 536-entry table kernel (cram_silu_mul): every gate bit pattern,
+    random up values, bit-equal to T(T(g / (1 + expf(-g))) * u) and to the small-input (formula) kernel."""
+    rows, inter = 4096, 4096  # 2M 16-byte items: above the table path's threshold
+    g = torch.Generator(device=DEV).manual_seed(5)
+    gate_bits = torch.randint(0, 65536, (rows, inter), device=DEV, generator=g, dtype=torch.int32)
+    gate_bits[:16].copy_(torch.arange(65536, device=DEV, dtype=torch.int32).view(16, 4096))  # every pattern at least once
+    gate = gate_bits.to(torch.int16).view(dtype)
+    up = (torch.randn(rows, inter, device=DEV, generator=g) * 2).to(dtype)
+    gu = torch.cat([gate, up], dim=1).contiguous()
+    got = ops.silu_mul(gu)
+    gf = gate.float()
+    want = ((gf / (1.0 + torch.exp(-gf))).to(dtype).float() * up.float()).to(dtype)
+    finite = torch.isfinite(gf)
+    same = (got.view(torch.int16) == want.view(torch.int16)) | ((got == 0) & (want == 0))
+    bad = finite & ~same & ~(torch.isnan(got.float()) & torch.isnan(want.float()))
+    assert int(bad.sum()) == 0, (gate[bad][:8], got[bad][:8], want[bad][:8])
+    small = torch.cat([ops.silu_mul(gu[i:i + 64].contiguous()) for i in range(0, 256, 64)])  # formula kernel
+    a, b = got[:256].view(torch.int16), small.view(torch.int16)
+    assert bool(((a == b) | ~finite[:256]).all())
