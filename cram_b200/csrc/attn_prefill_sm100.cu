@@ -386,10 +386,14 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
   constexpr uint32_t kIdescPV = ptx::umma_idesc_f16(kAbFmt, kBlockM, DH, 1);
 
   // ---- which tile pair ---------------------------------------------------------------------------
+  // CTA order: heads fastest (the 4 / 7 / 8 query heads of a KV head run side by side and share its tiles in L2), then
+  // the row-block pairs of ONE sequence, heaviest (latest rows) first, then the next sequence: all readers of a
+  // sequence's K / V (8.4 MB at 2k tokens) run within ~2 waves, so the tiles come from DRAM once. Pair-major order
+  // re-read them ~4x (the batch's 134 MB of K / V does not stay in the 126 MB L2 between pair indices).
   const int head = blockIdx.x % p.n_heads;
   const int rest = blockIdx.x / p.n_heads;
-  const int seq = rest % p.n_seq;
-  const int pair = num_pairs - 1 - rest / p.n_seq;  // heaviest (latest) query rows first
+  const int pair = num_pairs - 1 - rest % num_pairs;
+  const int seq = rest / num_pairs;
   const int q0 = p.cu_seqlens_q[seq], len_q = p.cu_seqlens_q[seq + 1] - q0;
   if (pair * kStages * kBlockM >= len_q) return;
   const int32_t* cuk = p.cu_seqlens_k ? p.cu_seqlens_k : p.cu_seqlens_q;
