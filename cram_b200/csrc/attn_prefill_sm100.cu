@@ -30,6 +30,7 @@
 // aliases the first half of S, so per stage the chain is softmax(j) -> P V(j) -> Q K^T(j+1) -> softmax(j+1).
 // Lazy O rescale (only when a row's max grows by more than 2^8) keeps the correction off the hot loop, and lets the
 // exponentials of a tile be issued speculatively against the standing reference max, in the pass that forms the scores.
+#include <atomic>
 #include <mutex>
 #include <type_traits>
 #include <utility>
@@ -47,6 +48,8 @@ constexpr int kBlockN = 128;  // keys per K/V tile
 constexpr int kKV = 2;        // K ring depth = V ring depth (32 KB per slot at d = 128)
 constexpr int kBiasRing = 4;  // bias vectors in flight (written with K[j], read until P V[j] is done)
 constexpr int kThreads = 384;
+constexpr int kSched = 4;           // scheduler ring depth (work items published ahead)
+constexpr int kItemConsumers = 10;  // MMA warp, bias warp, eight softmax warps (lane 0 of each frees a slot)
 constexpr int kTmemCols = 512;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
@@ -74,6 +77,8 @@ __device__ int g_trace_tile;
   } while (0)
 #endif
 
+__device__ unsigned g_work_counter[256];  // dynamic work queues of the persistent kernel, one per launch in flight
+
 struct Barriers {
   uint64_t q_full[2];
   uint64_t k_full[kKV], k_empty[kKV];
@@ -82,7 +87,8 @@ struct Barriers {
   uint64_t s_full[2];                   // [query stage] S(j) is complete (one phase per tile)
   uint64_t p_full[2][2];                // [query stage][half] P of that 64-key half is written (one phase per tile)
   uint64_t o_half[2];                   // [query stage] P V of the first half has completed (exact path of the second)
-  uint64_t o_done[2];                   // [query stage] one phase per P V (lazy-rescale wait)
+  uint64_t q_empty[2];                  // [query stage] the last Q K^T that reads this Q tile has completed
+  uint64_t item_full[kSched], item_empty[kSched];  // scheduler ring: work item published / read by every consumer
   uint64_t o_final[2];                  // [query stage] single phase: the last P V has completed
 };
 
@@ -96,7 +102,8 @@ struct Smem {
   static constexpr int kK = kQ + kStages * kQTileBytes;
   static constexpr int kV = kK + kKV * kTileBytes;
   static constexpr int kBias = kV + kKV * kTileBytes;
-  static constexpr int kBar = kBias + kBiasRing * kBlockN * 4;
+  static constexpr int kSched = kBias + kBiasRing * kBlockN * 4;  // Item [kSched]: decoded work items, published by the producer
+  static constexpr int kBar = kSched + cram::kSched * 64;
   static constexpr int kTmemPtr = kBar + (int)sizeof(Barriers);
   static constexpr int kEnd = kTmemPtr + 16;
   // dynamic smem request: + 1024 for manual alignment; padded above half an SM so that exactly one
@@ -374,46 +381,74 @@ __device__ __forceinline__ void issue_pv_steps(uint32_t o_tmem, uint32_t p_tmem,
    ...);
 }
 
+// ---- work items ------------------------------------------------------------------------------------------------
+// One item = 256 query rows (a pair of 128-row tiles) of one (sequence, head). Item order: heads fastest (the 4 / 7 / 8
+// query heads of a KV head run side by side and share its tiles in L2), then the row-block pairs of ONE sequence, heaviest
+// (latest rows) first, then the next sequence: all readers of a sequence's K / V (8.4 MB at 2k tokens) run within ~2 waves,
+// so the tiles come from DRAM once (pair-major order re-read them ~4x: 1079 MB per launch against 617 MB).
+struct alignas(16) Item {
+  int idx;  // position in the work list; >= n_items marks the end of the list
+  int head, kv_head, seq, pair, q0, len_q, k0, len_k, diag, nt[2], n_max;
+  int pad[3];
+};
+static_assert(sizeof(Item) == 64, "one scheduler-ring slot");
+
+__device__ __forceinline__ Item decode_item(const cram_attn_prefill_params& p, const int num_pairs, const int idx) {
+  Item w;
+  w.idx = idx;
+  w.head = idx % p.n_heads;
+  const int rest = idx / p.n_heads;
+  w.pair = num_pairs - 1 - rest % num_pairs;
+  w.seq = rest / num_pairs;
+  w.q0 = p.cu_seqlens_q[w.seq];
+  w.len_q = p.cu_seqlens_q[w.seq + 1] - w.q0;
+  const int32_t* cuk = p.cu_seqlens_k ? p.cu_seqlens_k : p.cu_seqlens_q;
+  w.k0 = cuk[w.seq];
+  w.len_k = cuk[w.seq + 1] - w.k0;
+  w.diag = w.len_k - w.len_q;  // query i sees keys <= i + diag
+  w.kv_head = w.head / (p.n_heads / p.n_kv_heads);
+#pragma unroll
+  for (int s = 0; s < kStages; ++s) {  // number of 128-key tiles query stage s visits
+    const int mt = w.pair * kStages + s;
+    int kv_end = w.len_k;
+    if (p.causal) kv_end = min(w.len_k, mt * kBlockM + kBlockM + w.diag);
+    w.nt[s] = (mt * kBlockM < w.len_q && kv_end > 0) ? (kv_end + kBlockN - 1) / kBlockN : 0;
+  }
+  w.n_max = max(w.nt[0], w.nt[1]);
+  return w;
+}
+
+// PERSISTENT kernel: one CTA per SM walks a dynamic queue of work items (atomic counter; the first item of a CTA is its
+// block index). TMEM, the barriers and the K / V / bias rings live across items: the producer runs into the next item's
+// Q / K / V while the softmax warps finish the current one, the MMA warp issues the next item's first Q K^T right behind
+// the last P V of the current one, and the epilogue of item i overlaps the first tensor work of item i+1. All ring / phase counters are running counts over the CTA's stream of
+// tiles; every role derives them from the same item sequence.
 template <typename T, int DH>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                           const __grid_constant__ CUtensorMap tmap_v, const cram_attn_prefill_params p,
-                          const int num_pairs) {
+                          const int num_pairs, const int n_items, unsigned* __restrict__ work_counter) {
   using S = Smem<DH>;
   constexpr int kSlabs = DH / 64;
   constexpr uint32_t kAbFmt = DType<T>::code == CRAM_BF16 ? 1u : 0u;
   constexpr uint32_t kIdescQK = ptx::umma_idesc_f16(kAbFmt, kBlockM, kBlockN, 0);
   constexpr uint32_t kIdescPV = ptx::umma_idesc_f16(kAbFmt, kBlockM, DH, 1);
 
-  // ---- which tile pair ---------------------------------------------------------------------------
-  // CTA order: heads fastest (the 4 / 7 / 8 query heads of a KV head run side by side and share its tiles in L2), then
-  // the row-block pairs of ONE sequence, heaviest (latest rows) first, then the next sequence: all readers of a
-  // sequence's K / V (8.4 MB at 2k tokens) run within ~2 waves, so the tiles come from DRAM once. Pair-major order
-  // re-read them ~4x (the batch's 134 MB of K / V does not stay in the 126 MB L2 between pair indices).
-  const int head = blockIdx.x % p.n_heads;
-  const int rest = blockIdx.x / p.n_heads;
-  const int pair = num_pairs - 1 - rest % num_pairs;
-  const int seq = rest / num_pairs;
-  const int q0 = p.cu_seqlens_q[seq], len_q = p.cu_seqlens_q[seq + 1] - q0;
-  if (pair * kStages * kBlockM >= len_q) return;
-  const int32_t* cuk = p.cu_seqlens_k ? p.cu_seqlens_k : p.cu_seqlens_q;
-  const int k0 = cuk[seq], len_k = cuk[seq + 1] - k0;
-  const int diag = len_k - len_q;  // query i sees keys <= i + diag
-  const int kv_head = head / (p.n_heads / p.n_kv_heads);
-  auto tiles_of = [&](int s) {  // number of 64-key tiles query stage s visits
-    const int mt = pair * kStages + s;
-    int kv_end = len_k;
-    if (p.causal) kv_end = min(len_k, mt * kBlockM + kBlockM + diag);
-    return (mt * kBlockM < len_q && kv_end > 0) ? (kv_end + kBlockN - 1) / kBlockN : 0;
-  };
-  const int n_t0 = tiles_of(0), n_t1 = tiles_of(1);
-  const int n_max = max(n_t0, n_t1);
-
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   Barriers* bar = reinterpret_cast<Barriers*>(smem + S::kBar);
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + S::kTmemPtr);
   float* s_bias = reinterpret_cast<float*>(smem + S::kBias);
+  Item* s_items = reinterpret_cast<Item*>(smem + S::kSched);
+  // copy a ring slot to registers / from registers (4 x 16 bytes)
+  auto read_slot = [&](int slot) {
+    Item w;
+    const uint4* src = reinterpret_cast<const uint4*>(&s_items[slot]);
+    uint4* dst = reinterpret_cast<uint4*>(&w);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i] = src[i];
+    return w;
+  };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -423,7 +458,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     ptx::prefetch_tmap(&tmap_v);
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&bar->q_full[i], 1);
-      ptx::mbar_init(&bar->o_done[i], 1);
+      ptx::mbar_init(&bar->q_empty[i], 1);
       ptx::mbar_init(&bar->o_final[i], 1);
       ptx::mbar_init(&bar->s_full[i], 1);
       ptx::mbar_init(&bar->p_full[i][0], kBlockM);
@@ -437,27 +472,11 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       ptx::mbar_init(&bar->v_empty[i], 1);
     }
     for (int i = 0; i < kBiasRing; ++i) ptx::mbar_init(&bar->bias_full[i], 1);
+    for (int i = 0; i < kSched; ++i) {
+      ptx::mbar_init(&bar->item_full[i], 1);
+      ptx::mbar_init(&bar->item_empty[i], kItemConsumers);
+    }
     ptx::fence_mbar_init();
-    // First loads (Q of both stages, K[0], K[1]) go out now: their HBM/L2 latency overlaps the TMEM allocation,
-    // the CTA-wide sync and the role dispatch instead of following them.
-#pragma unroll
-    for (int s = 0; s < kStages; ++s) {
-      if ((s ? n_t1 : n_t0) == 0) continue;
-      ptx::mbar_expect_tx(&bar->q_full[s], S::kQTileBytes);
-#pragma unroll
-      for (int sl = 0; sl < kSlabs; ++sl)
-        ptx::tma_load_2d_hint(smem + S::kQ + s * S::kQTileBytes + sl * S::kQSlabBytes, &tmap_q, &bar->q_full[s],
-                              head * DH + sl * 64, q0 + (pair * kStages + s) * kBlockM, ptx::kL2EvictFirst);
-    }
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      if (j >= n_max) continue;
-      ptx::mbar_expect_tx(&bar->k_full[j], S::kTileBytes);
-#pragma unroll
-      for (int sl = 0; sl < kSlabs; ++sl)
-        ptx::tma_load_2d_hint(smem + S::kK + j * S::kTileBytes + sl * S::kSlabBytes, &tmap_k, &bar->k_full[j],
-                              kv_head * DH + sl * 64, k0 + j * kBlockN, ptx::kL2EvictLast);
-    }
   }
   if (warp == 9) ptx::tmem_alloc(tmem_ptr_smem, kTmemCols);
   ptx::tc_fence_before();
@@ -465,128 +484,240 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
+  // Every consumer role walks the same item sequence: entry `it` of the scheduler ring. The items arrive DECODED (the
+  // producer did the cu_seqlens loads and the divisions while it was running ahead), one 64-byte broadcast read per warp.
+  auto next_item = [&](int it) -> Item {
+    const int slot = it % kSched;
+    ptx::mbar_wait(&bar->item_full[slot], (it / kSched) & 1);
+    const Item w = read_slot(slot);
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive(&bar->item_empty[slot]);
+    return w;
+  };
+
   if (warp >= 8) {
     setmaxnreg_dec<56>();
     if (warp == 8) {
-      // ============================== producer ==================================================
-      // Order K[0], K[1] (before the CTA-wide sync), then per step j: V[j], K[j+2]. A slot is re-filled as soon as the
-      // last MMA that reads it has completed (k_empty / v_empty are tcgen05.commit arrivals).
-      for (int j = 0; j < n_max; ++j) {
-        if (lane == 0) {
-          const int st = j % kKV;
-          CRAM_TRACE(10, j, 0);
-          ptx::mbar_wait(&bar->v_empty[st], ((j / kKV) & 1) ^ 1);
-          CRAM_TRACE(10, j, 1);
-          ptx::mbar_expect_tx(&bar->v_full[st], S::kTileBytes);
+      // ============================== scheduler + producer =======================================
+      // Per item: Q of both stages (once the previous item's last Q K^T of that stage has completed), K[0], K[1], then per
+      // tile j: V[j], K[j+2]. gt = running tile count: ring slot gt % kKV, phase gt / kKV. A slot is re-filled as soon as
+      // the last MMA that reads it has completed (k_empty / v_empty are tcgen05.commit arrivals).
+      int gt = 0, qi[2] = {0, 0};
+      // publish entry `it` of the scheduler ring (lane 0)
+      auto publish = [&](int it, const Item& w) {
+        const int slot = it % kSched;
+        if (it >= kSched) ptx::mbar_wait(&bar->item_empty[slot], ((it / kSched) & 1) ^ 1);
+        const uint4* src = reinterpret_cast<const uint4*>(&w);
+        uint4* dst = reinterpret_cast<uint4*>(&s_items[slot]);
 #pragma unroll
-          for (int sl = 0; sl < kSlabs; ++sl)
-            ptx::tma_load_2d_hint(smem + S::kV + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_v, &bar->v_full[st],
-                                  kv_head * DH + sl * 64, k0 + j * kBlockN, ptx::kL2EvictLast);
-          CRAM_TRACE(10, j, 2);
-          if (j + 2 < n_max) {
-            ptx::mbar_wait(&bar->k_empty[st], (((j + 2) / kKV) & 1) ^ 1);
+        for (int i = 0; i < 4; ++i) dst[i] = src[i];
+        ptx::mbar_arrive(&bar->item_full[slot]);
+      };
+      // Next work item that has query rows (items of a ragged batch whose row block lies past the end of their sequence
+      // are never published: every published entry is either real work or the end marker, which is what lets the MMA
+      // warp read exactly one entry ahead). The first item of a CTA is its block index, the rest come from the queue.
+      bool first = true;
+#ifdef CRAM_ABL_STATIC_QUEUE
+      int static_next = (int)blockIdx.x;
+#endif
+      auto take = [&]() -> Item {
+        for (;;) {
+#ifdef CRAM_ABL_STATIC_QUEUE
+          static_next += first ? 0 : (int)gridDim.x;
+          const int i = first ? (int)blockIdx.x : static_next;
+#else
+          const int i = first ? (int)blockIdx.x : (int)(atomicAdd(work_counter, 1u) + gridDim.x);
+#endif
+          first = false;
+          if (i >= n_items) {
+            Item e = {};
+            e.idx = n_items;
+            return e;
+          }
+          const Item w = decode_item(p, num_pairs, i);
+          if (w.pair * kStages * kBlockM < w.len_q) return w;
+        }
+      };
+      // lane 0 runs the queue and the loads; the whole warp only meets at the end
+      if (lane == 0) {
+        Item w = take();
+        publish(0, w);
+        for (int it = 0; w.idx < n_items; ++it) {
+          // The NEXT item is published before this item's loads are issued: the MMA warp reads one item ahead (it issues
+          // the next item's first Q K^T behind this item's last P V), and this item's loads wait for ring slots that
+          // only the MMA warp frees.
+          const Item w_next = take();
+          publish(it + 1, w_next);
+          if (w.n_max > 0) {  // n_max = 0: rows that see no key at all (len_k < len_q); the softmax warps write zeros
+          auto load_k = [&](int j) {
+            const int g = gt + j, st = g % kKV;
+            ptx::mbar_wait(&bar->k_empty[st], ((g / kKV) & 1) ^ 1);
             ptx::mbar_expect_tx(&bar->k_full[st], S::kTileBytes);
 #pragma unroll
             for (int sl = 0; sl < kSlabs; ++sl)
               ptx::tma_load_2d_hint(smem + S::kK + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_k, &bar->k_full[st],
-                                    kv_head * DH + sl * 64, k0 + (j + 2) * kBlockN, ptx::kL2EvictLast);
+                                    w.kv_head * DH + sl * 64, w.k0 + j * kBlockN, ptx::kL2EvictLast);
+          };
+          // K[0] goes out before the Q tiles: it only needs a free ring slot, while a Q tile has to wait for the previous
+          // item's last Q K^T of its stage.
+          load_k(0);
+#pragma unroll
+          for (int s = 0; s < kStages; ++s) {
+            if (w.nt[s] == 0) continue;
+            if (qi[s] > 0) ptx::mbar_wait(&bar->q_empty[s], (qi[s] - 1) & 1);
+            ++qi[s];
+            ptx::mbar_expect_tx(&bar->q_full[s], S::kQTileBytes);
+#pragma unroll
+            for (int sl = 0; sl < kSlabs; ++sl)
+              ptx::tma_load_2d_hint(smem + S::kQ + s * S::kQTileBytes + sl * S::kQSlabBytes, &tmap_q, &bar->q_full[s],
+                                    w.head * DH + sl * 64, w.q0 + (w.pair * kStages + s) * kBlockM, ptx::kL2EvictFirst);
           }
-          CRAM_TRACE(10, j, 3);
+          if (w.n_max > 1) load_k(1);
+          for (int j = 0; j < w.n_max; ++j) {
+            const int g = gt + j, st = g % kKV;
+            ptx::mbar_wait(&bar->v_empty[st], ((g / kKV) & 1) ^ 1);
+            ptx::mbar_expect_tx(&bar->v_full[st], S::kTileBytes);
+#pragma unroll
+            for (int sl = 0; sl < kSlabs; ++sl)
+              ptx::tma_load_2d_hint(smem + S::kV + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_v, &bar->v_full[st],
+                                    w.kv_head * DH + sl * 64, w.k0 + j * kBlockN, ptx::kL2EvictLast);
+            if (j + 2 < w.n_max) load_k(j + 2);
+          }
+          }
+          gt += w.n_max;
+          w = w_next;
         }
-        __syncwarp();
       }
+      __syncwarp();
     } else if (warp == 10) {
       // ============================== bias vectors ===============================================
       // Its own warp (on a different sub-partition than the TMA producer): the log-credibility loads are dependent
-      // global loads, and behind the TMA issue they kept the producer from running ahead. The vector of tile j
-      // (already x log2e, -inf past the key length) lives in a ring of 4 until every P V[j] is done; tile j is
-      // written once the V slot of tile j-2 has been seen free (the producer's own condition for V[j], so the phase
+      // global loads, and behind the TMA issue they kept the producer from running ahead. The vector of tile g
+      // (already x log2e, -inf past the key length) lives in a ring of 4 until every P V[g] is done; tile g is
+      // written once the V slot of tile g-2 has been seen free (the producer's own condition for V[g], so the phase
       // parity cannot alias: that barrier's next completion needs this very vector) -- two tiles of slack.
-      const bool biased = p.logcred != nullptr && ((p.head_mask >> head) & 1ull);
-      const int bias_len = p.bias_len ? p.bias_len[seq] : len_k;
-      for (int j = 0; j < n_max; ++j) {
-        if (j >= kKV) ptx::mbar_wait(&bar->v_empty[j % kKV], ((j / kKV) & 1) ^ 1);
-        float4 b4;
-        float* bp = reinterpret_cast<float*>(&b4);
+      int gt = 0;
+      for (int it = 0;; ++it) {
+        const Item w = next_item(it);
+        if (w.idx >= n_items) break;
+        const bool biased = p.logcred != nullptr && ((p.head_mask >> w.head) & 1ull);
+        const int bias_len = p.bias_len ? p.bias_len[w.seq] : w.len_k;
+        for (int j = 0; j < w.n_max; ++j) {
+          const int g = gt + j;
+          if (g >= kKV) ptx::mbar_wait(&bar->v_empty[g % kKV], ((g / kKV) & 1) ^ 1);
+          float4 b4;
+          float* bp = reinterpret_cast<float*>(&b4);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int key = j * kBlockN + lane * 4 + e;
-          float v = 0.f;
-          if (key >= len_k) v = -INFINITY;
-          else if (biased && key < bias_len) v = load_logcred(p.logcred, (int64_t)k0 + key, p.logcred_dtype) * kLog2e;
-          bp[e] = v;
+          for (int e = 0; e < 4; ++e) {
+            const int key = j * kBlockN + lane * 4 + e;
+            float v = 0.f;
+            if (key >= w.len_k) v = -INFINITY;
+            else if (biased && key < bias_len) v = load_logcred(p.logcred, (int64_t)w.k0 + key, p.logcred_dtype) * kLog2e;
+            bp[e] = v;
+          }
+          reinterpret_cast<float4*>(s_bias + (g % kBiasRing) * kBlockN)[lane] = b4;
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&bar->bias_full[g % kBiasRing]);
         }
-        reinterpret_cast<float4*>(s_bias + (j % kBiasRing) * kBlockN)[lane] = b4;
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&bar->bias_full[j % kBiasRing]);
+        gt += w.n_max;
       }
     } else if (warp == 9 && ptx::elect_one_sync()) {
-      // ============================== MMA issuer ================================================
+      // ============================== MMA issuer (one elected lane) ==============================
       // Per query stage s the chain is Q K^T(j) -> softmax(j) -> P V(j) -> Q K^T(j+1): S is single-buffered and P
       // aliases it, the tensor pipe executes in order, so Q K^T(j+1) issued behind P V(j) cannot overtake it. While
-      // stage s waits for its softmax, the pipe runs the other stage's P V + Q K^T (1024 cycles at d = 128).
+      // stage s waits for its softmax, the pipe runs the other stage's P V + Q K^T (1024 cycles at d = 128). Behind the
+      // last P V of an item comes the first Q K^T of the NEXT item (both stages).
       const uint32_t q_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + S::kQ), 16);
       const uint32_t k_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + S::kK), 16);
       const uint32_t v_lo = ptx::umma_desc_lo(ptx::smem_u32(smem + S::kV), S::kSlabBytes);
       constexpr uint32_t kQTile16 = S::kQTileBytes >> 4;
       constexpr uint32_t kTile16 = S::kTileBytes >> 4;
-      auto issue_qk = [&](int s, int j) {
-        const int st = j % kKV;
-        ptx::mbar_wait(&bar->k_full[st], (j / kKV) & 1);
+      int it = 0, tc[2] = {0, 0}, qc[2] = {0, 0};
+      // next item of the sequence that has tiles (this lane is the warp's only consumer of the scheduler ring)
+      auto fetch = [&](Item& w) -> bool {
+        const int slot = it % kSched;
+        ptx::mbar_wait(&bar->item_full[slot], (it / kSched) & 1);
+        w = read_slot(slot);
+        ptx::mbar_arrive(&bar->item_empty[slot]);
+        ++it;
+        return w.idx < n_items;  // an item without tiles (n_max = 0) simply passes through the loops below
+      };
+      // Q K^T of tile j of item w (whose first tile is global tile g0) for stage s
+      auto issue_qk = [&](int s, const Item& w, int g0, int j) {
+        const int g = g0 + j, st = g % kKV;
+        if (j == 0) {
+          ptx::mbar_wait(&bar->q_full[s], qc[s] & 1);
+          ++qc[s];
+        }
+        ptx::mbar_wait(&bar->k_full[st], (g / kKV) & 1);
         ptx::tc_fence_after();
         issue_qk_steps(tmem_base + s * 128, q_lo + s * kQTile16, k_lo + st * kTile16, kIdescQK,
                        std::make_integer_sequence<int, DH / 16>{});
         ptx::tc_commit(&bar->s_full[s]);
-        if (s == 1 || j >= n_t1) ptx::tc_commit(&bar->k_empty[st]);  // last stage to read K[j]
+        if (s == 1 || j >= w.nt[1]) ptx::tc_commit(&bar->k_empty[st]);  // last stage to read K[j]
+        if (j == w.nt[s] - 1) ptx::tc_commit(&bar->q_empty[s]);         // last Q K^T that reads this item's Q tile
       };
+      Item cur, nxt;
+      bool have = fetch(cur);
+      int gt = 0;
+      if (have) {
 #pragma unroll
-      for (int s = 0; s < kStages; ++s)
-        if ((s ? n_t1 : n_t0) > 0) {
-          ptx::mbar_wait(&bar->q_full[s], 0);
-          issue_qk(s, 0);
-        }
-      for (int j = 0; j < n_max; ++j) {
-        const int st = j % kKV;
+        for (int s = 0; s < kStages; ++s)
+          if (cur.nt[s] > 0) issue_qk(s, cur, gt, 0);
+      }
+      while (have) {
+        const bool have_next = fetch(nxt);
+        const int gt_next = gt + cur.n_max;
+        for (int j = 0; j < cur.n_max; ++j) {
+          const int g = gt + j, st = g % kKV;
 #pragma unroll
-        for (int s = 0; s < kStages; ++s) {
-          const int nt = s ? n_t1 : n_t0;
-          if (j >= nt) continue;
-          CRAM_TRACE(8 + s, j, 0);
-          ptx::mbar_wait(&bar->v_full[st], (j / kKV) & 1);
-          CRAM_TRACE(8 + s, j, 1);
-          ptx::mbar_wait(&bar->p_full[s][0], j & 1);
-          ptx::tc_fence_after();
-          issue_pv_steps<0>(tmem_base + 256 + s * 128, tmem_base + s * 128, v_lo + st * kTile16, kIdescPV, j > 0,
-                            std::make_integer_sequence<int, kBlockN / 32>{});
-          ptx::tc_commit(&bar->o_half[s]);
-          ptx::mbar_wait(&bar->p_full[s][1], j & 1);
-          ptx::tc_fence_after();
-          CRAM_TRACE(8 + s, j, 2);
-          issue_pv_steps<kBlockN / 32>(tmem_base + 256 + s * 128, tmem_base + s * 128, v_lo + st * kTile16, kIdescPV, true,
-                                       std::make_integer_sequence<int, kBlockN / 32>{});
-          ptx::tc_commit(&bar->o_done[s]);
-          if (j == nt - 1) ptx::tc_commit(&bar->o_final[s]);
-          if (s == 1 || j >= n_t1) ptx::tc_commit(&bar->v_empty[st]);  // last stage to read V[j]
-          if (j + 1 < nt) issue_qk(s, j + 1);
-          CRAM_TRACE(8 + s, j, 3);
+          for (int s = 0; s < kStages; ++s) {
+            const int nt = cur.nt[s];
+            if (j >= nt) continue;
+            ptx::mbar_wait(&bar->v_full[st], (g / kKV) & 1);
+            ptx::mbar_wait(&bar->p_full[s][0], tc[s] & 1);
+            ptx::tc_fence_after();
+            issue_pv_steps<0>(tmem_base + 256 + s * 128, tmem_base + s * 128, v_lo + st * kTile16, kIdescPV, j > 0,
+                              std::make_integer_sequence<int, kBlockN / 32>{});
+            ptx::tc_commit(&bar->o_half[s]);
+            ptx::mbar_wait(&bar->p_full[s][1], tc[s] & 1);
+            ptx::tc_fence_after();
+            issue_pv_steps<kBlockN / 32>(tmem_base + 256 + s * 128, tmem_base + s * 128, v_lo + st * kTile16, kIdescPV, true,
+                                         std::make_integer_sequence<int, kBlockN / 32>{});
+            if (j == nt - 1) ptx::tc_commit(&bar->o_final[s]);
+            if (s == 1 || j >= cur.nt[1]) ptx::tc_commit(&bar->v_empty[st]);  // last stage to read V[j]
+            ++tc[s];
+            if (j + 1 < nt) issue_qk(s, cur, gt, j + 1);
+          }
         }
+        // The next item's first Q K^T of both stages goes out HERE, behind the last P V of the whole item, not behind the
+        // last P V of each stage: chaining stage 0's (it finishes a tile earlier in a causal item) put 512 tensor cycles
+        // in front of stage 1's last P V + Q K^T, the critical path of the item's end. Measured at 16 x 2048 causal:
+        // 802 TFLOP/s chained (blocking on the next Q / K[0]), 841 chained only when both had landed, 896-904 not chained.
+        if (have_next) {
+#pragma unroll
+          for (int s = 0; s < kStages; ++s)
+            if (nxt.nt[s] > 0) issue_qk(s, nxt, gt_next, 0);
+        }
+        gt = gt_next;
+        cur = nxt;
+        have = have_next;
       }
     }
+    // warp 11 and the other lanes of warp 9 idle: kItemConsumers counts the MMA lane, the bias warp and the eight
+    // softmax warps
   } else {
     // ============================== softmax / correction / epilogue ================================
     setmaxnreg_inc<224>();
     const int s = warp >> 2;                      // query stage of this warpgroup
     const int row = (warp & 3) * 32 + lane;       // row inside the tile == TMEM lane
-    const int mt = pair * kStages + s;
-    const int qrow = mt * kBlockM + row;          // row inside the sequence
     const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t s_base = tmem_base + lane_off + s * 128;
     const uint32_t o_addr = tmem_base + lane_off + 256 + s * 128;
     const float scale2 = p.scale * kLog2e;
     const uint32_t bias_addr = ptx::smem_u32(s_bias);
-    const int nt = s ? n_t1 : n_t0;
-    float m_ref = -INFINITY, m_next = -INFINITY, l = 0.f;
     const uint64_t sc2 = pk2(scale2, scale2);
+    int gt = 0, tc = 0, ic = 0;  // running counts: tiles of the CTA, tiles of this stage, items of this stage
 
     // hand a half of P over to the MMA warp: its tcgen05.st must have completed
     auto release = [&](int h) {
@@ -595,95 +726,103 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       ptx::mbar_arrive(&bar->p_full[s][h]);
     };
 
-    for (int j = 0; j < nt; ++j) {
-      const int bs = j % kBiasRing;
-      if (lane == 0) CRAM_TRACE(warp, j, 0);
-      ptx::mbar_wait(&bar->bias_full[bs], (j / kBiasRing) & 1);
-      ptx::mbar_wait(&bar->s_full[s], j & 1);
-      ptx::tc_fence_after();
-      if (lane == 0) CRAM_TRACE(warp, j, 1);
-      const bool diag_tile = p.causal && (j * kBlockN + kBlockN - 1 > mt * kBlockM + diag);
-      const int climit = qrow + diag - j * kBlockN;  // columns <= climit are visible
-      const uint32_t b_addr = bias_addr + bs * kBlockN * 4;
+    for (int it = 0;; ++it) {
+      const Item w = next_item(it);
+      if (w.idx >= n_items) break;
+      const int mt = w.pair * kStages + s;
+      const int qrow = mt * kBlockM + row;          // row inside the sequence
+      const int nt = w.nt[s];
+      float m_ref = -INFINITY, m_next = -INFINITY, l = 0.f;
 
-      auto tile = [&](auto diag_tag) {
-        constexpr bool kDiag = decltype(diag_tag)::value;
-        if (j == 0) {
-          // reference of a fresh row block: the max of its first 32 keys (column 0 is visible to every row)
-          m_ref = chunks_max<kDiag>(s_base, b_addr, sc2, climit, 0, 1);
-          m_next = m_ref;
-        } else {
-          // delayed lazy rescale: a row whose previous tile asked for a larger reference moves now. s_full(j) has been
-          // observed and Q K^T(j) was issued behind P V(j-1), so O holds every product up to tile j-1.
-          const bool pend = m_next > m_ref;
-          if (__any_sync(0xffffffffu, pend)) {
-            rescale_o<DH>(o_addr, pend ? ex2(m_ref - m_next) : 1.0f, l);
-            m_ref = m_next;
-          }
-        }
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          uint32_t pk[32];
-          const float sum = spec_half<T, kDiag>(s_base, b_addr, sc2, climit, m_ref, h, pk, [&] {
-            if (h == 1) release(0);  // P of the first half was stored one chunk ago
-          });
-          // a row with no reference yet (every key so far masked out or of zero credibility) that now sees one
-          const bool exact = !(sum < ExactAbove<T>::value) || (m_ref == -INFINITY && sum > 0.f);
-          if (__any_sync(0xffffffffu, exact)) {
-            // exact path (rare). O must hold every product issued so far before it is rescaled.
-            const float mx = chunks_max<kDiag>(s_base, b_addr, sc2, climit, 2 * h, 2 * h + 2);
-            const float m_new = exact ? fmaxf(mx, m_ref) : m_ref;
-            if (h == 1) {
-              ptx::mbar_wait(&bar->o_half[s], j & 1);
-              ptx::tc_fence_after();
-            }
-            if (j > 0 || h == 1) rescale_o<DH>(o_addr, (m_new > m_ref) ? ex2(m_ref - m_new) : 1.0f, l);
-            m_ref = m_new;
-            m_next = fmaxf(m_next, m_ref);
-            l += exact_pass<T, kDiag>(s_base, b_addr, sc2, climit, m_ref, 2 * h, 2 * h + 2);
+      for (int j = 0; j < nt; ++j, ++tc) {
+        const int g = gt + j, bs = g % kBiasRing;
+        ptx::mbar_wait(&bar->bias_full[bs], (g / kBiasRing) & 1);
+        ptx::mbar_wait(&bar->s_full[s], tc & 1);
+        ptx::tc_fence_after();
+        const bool diag_tile = p.causal && (j * kBlockN + kBlockN - 1 > mt * kBlockM + w.diag);
+        const int climit = qrow + w.diag - j * kBlockN;  // columns <= climit are visible
+        const uint32_t b_addr = bias_addr + bs * kBlockN * 4;
+
+        auto tile = [&](auto diag_tag) {
+          constexpr bool kDiag = decltype(diag_tag)::value;
+          if (j == 0) {
+            // reference of a fresh row block: the max of its first 32 keys (column 0 is visible to every row)
+            m_ref = chunks_max<kDiag>(s_base, b_addr, sc2, climit, 0, 1);
+            m_next = m_ref;
           } else {
-            ptx::tmem_st32(s_base + h * 32, pk);
-            l += sum;
-            if (!(sum < kSoftAbove)) m_next = fmaxf(m_next, m_ref + __log2f(sum));  // >= the true max of this half
+            // delayed lazy rescale: a row whose previous tile asked for a larger reference moves now. s_full(j) has been
+            // observed and Q K^T(j) was issued behind P V(j-1), so O holds every product up to tile j-1.
+            const bool pend = m_next > m_ref;
+            if (__any_sync(0xffffffffu, pend)) {
+              rescale_o<DH>(o_addr, pend ? ex2(m_ref - m_next) : 1.0f, l);
+              m_ref = m_next;
+            }
           }
-          if (h == 1) release(1);
-        }
-      };
-      if (diag_tile) tile(std::true_type{});
-      else tile(std::false_type{});
-      if (lane == 0) CRAM_TRACE(warp, j, 3);
-    }
-
-    // ---- epilogue: O / l -> global ---------------------------------------------------------------
-    const bool row_ok = qrow < len_q;
-    T* out = reinterpret_cast<T*>(p.out) + (int64_t)(q0 + qrow) * p.out_row_stride + (int64_t)head * DH;
-    if (nt > 0) {
-      ptx::mbar_wait(&bar->o_final[s], 0);  // committed after the last P V of this stage
-      ptx::tc_fence_after();
-      const float inv = l > 0.f ? 1.0f / l : 0.f;
 #pragma unroll
-      for (int c = 0; c < DH / 32; ++c) {
-        uint32_t o[32];
-        ptx::tmem_ld32(o_addr + c * 32, o);
-        ptx::tc_wait_ld();
-        if (row_ok) {
-#pragma unroll
-          for (int i = 0; i < 32; i += 8) {
-            uint4 v;
-            v.x = pack2<T>(__uint_as_float(o[i + 0]) * inv, __uint_as_float(o[i + 1]) * inv);
-            v.y = pack2<T>(__uint_as_float(o[i + 2]) * inv, __uint_as_float(o[i + 3]) * inv);
-            v.z = pack2<T>(__uint_as_float(o[i + 4]) * inv, __uint_as_float(o[i + 5]) * inv);
-            v.w = pack2<T>(__uint_as_float(o[i + 6]) * inv, __uint_as_float(o[i + 7]) * inv);
-            __stcs(reinterpret_cast<uint4*>(out + c * 32 + i), v);  // written once, read by the next kernel: do not displace K / V in L2
+          for (int h = 0; h < 2; ++h) {
+            uint32_t pk[32];
+            const float sum = spec_half<T, kDiag>(s_base, b_addr, sc2, climit, m_ref, h, pk, [&] {
+              if (h == 1) release(0);  // P of the first half was stored one chunk ago
+            });
+            // a row with no reference yet (every key so far masked out or of zero credibility) that now sees one
+            const bool exact = !(sum < ExactAbove<T>::value) || (m_ref == -INFINITY && sum > 0.f);
+            if (__any_sync(0xffffffffu, exact)) {
+              // exact path (rare). O must hold every product issued so far before it is rescaled.
+              const float mx = chunks_max<kDiag>(s_base, b_addr, sc2, climit, 2 * h, 2 * h + 2);
+              const float m_new = exact ? fmaxf(mx, m_ref) : m_ref;
+              if (h == 1) {
+                ptx::mbar_wait(&bar->o_half[s], tc & 1);
+                ptx::tc_fence_after();
+              }
+              if (j > 0 || h == 1) rescale_o<DH>(o_addr, (m_new > m_ref) ? ex2(m_ref - m_new) : 1.0f, l);
+              m_ref = m_new;
+              m_next = fmaxf(m_next, m_ref);
+              l += exact_pass<T, kDiag>(s_base, b_addr, sc2, climit, m_ref, 2 * h, 2 * h + 2);
+            } else {
+              ptx::tmem_st32(s_base + h * 32, pk);
+              l += sum;
+              if (!(sum < kSoftAbove)) m_next = fmaxf(m_next, m_ref + __log2f(sum));  // >= the true max of this half
+            }
+            if (h == 1) release(1);
           }
-        }
+        };
+        if (diag_tile) tile(std::true_type{});
+        else tile(std::false_type{});
       }
-      if (p.lse && row_ok)
-        p.lse[(int64_t)head * p.total_q + q0 + qrow] = l > 0.f ? (m_ref + log2f(l)) * 0.6931471805599453f : -INFINITY;
-    } else if (row_ok) {
+      gt += w.n_max;
+
+      // ---- epilogue: O / l -> global ---------------------------------------------------------------
+      const bool row_ok = qrow < w.len_q;
+      T* out = reinterpret_cast<T*>(p.out) + (int64_t)(w.q0 + qrow) * p.out_row_stride + (int64_t)w.head * DH;
+      if (nt > 0) {
+        ptx::mbar_wait(&bar->o_final[s], ic & 1);  // committed after the last P V of this stage and item
+        ++ic;
+        ptx::tc_fence_after();
+        const float inv = l > 0.f ? 1.0f / l : 0.f;
 #pragma unroll
-      for (int c = 0; c < DH; c += 8) *reinterpret_cast<uint4*>(out + c) = make_uint4(0, 0, 0, 0);
-      if (p.lse) p.lse[(int64_t)head * p.total_q + q0 + qrow] = -INFINITY;
+        for (int c = 0; c < DH / 32; ++c) {
+          uint32_t o[32];
+          ptx::tmem_ld32(o_addr + c * 32, o);
+          ptx::tc_wait_ld();
+          if (row_ok) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 8) {
+              uint4 v;
+              v.x = pack2<T>(__uint_as_float(o[i + 0]) * inv, __uint_as_float(o[i + 1]) * inv);
+              v.y = pack2<T>(__uint_as_float(o[i + 2]) * inv, __uint_as_float(o[i + 3]) * inv);
+              v.z = pack2<T>(__uint_as_float(o[i + 4]) * inv, __uint_as_float(o[i + 5]) * inv);
+              v.w = pack2<T>(__uint_as_float(o[i + 6]) * inv, __uint_as_float(o[i + 7]) * inv);
+              __stcs(reinterpret_cast<uint4*>(out + c * 32 + i), v);  // written once, read by the next kernel
+            }
+          }
+        }
+        if (p.lse && row_ok)
+          p.lse[(int64_t)w.head * p.total_q + w.q0 + qrow] = l > 0.f ? (m_ref + log2f(l)) * 0.6931471805599453f : -INFINITY;
+      } else if (row_ok) {
+#pragma unroll
+        for (int c = 0; c < DH; c += 8) *reinterpret_cast<uint4*>(out + c) = make_uint4(0, 0, 0, 0);
+        if (p.lse) p.lse[(int64_t)w.head * p.total_q + w.q0 + qrow] = -INFINITY;
+      }
     }
   }
 
@@ -741,16 +880,23 @@ int launch_t(const cram_attn_prefill_params& p, cudaStream_t stream) {
   if ((rc = make_tmap(&tk, p.k, p.dtype, (int64_t)p.n_kv_heads * DH, p.total_k, p.k_row_stride, kBlockN)) != CRAM_OK) return rc;
   if ((rc = make_tmap(&tv, p.v, p.dtype, (int64_t)p.n_kv_heads * DH, p.total_k, p.v_row_stride, kBlockN)) != CRAM_OK) return rc;
   const int num_pairs = (p.max_seqlen_q + kStages * kBlockM - 1) / (kStages * kBlockM);
-  const long long grid = (long long)num_pairs * p.n_seq * p.n_heads;
-  if (grid == 0) return CRAM_OK;
-  CRAM_REQUIRE(grid < (1ll << 31), "cram_attn_prefill: grid too large");
+  const long long n_items = (long long)num_pairs * p.n_seq * p.n_heads;
+  if (n_items == 0) return CRAM_OK;
+  CRAM_REQUIRE(n_items < (1ll << 30), "cram_attn_prefill: too many work items");
   auto kern = attn_prefill_sm100_kernel<T, DH>;
   static PerDeviceOnce attr;  // per template instantiation, per device
   if (!attr.flag()) {
     CRAM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<DH>::kRequest));
     attr.flag() = true;
   }
-  kern<<<(unsigned)grid, kThreads, Smem<DH>::kRequest, stream>>>(tq, tk, tv, p, num_pairs);
+  // dynamic work queue: one counter per launch out of a ring of 256 module globals, zeroed on the launching stream
+  static std::atomic<unsigned> launch_seq{0};
+  unsigned* counters = nullptr;
+  CRAM_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&counters), g_work_counter));
+  unsigned* counter = counters + (launch_seq.fetch_add(1) & 255u);
+  CRAM_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned), stream));
+  const int grid = (int)(n_items < sm_count() ? n_items : sm_count());
+  kern<<<grid, kThreads, Smem<DH>::kRequest, stream>>>(tq, tk, tv, p, num_pairs, (int)n_items, counter);
   return check_launch("attn_prefill_sm100_kernel");
 }
 

@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda.h>  // CUtensorMap (types only; the driver is reached through cudaGetDriverEntryPoint)
 #include <stdint.h>
+#include <stdio.h>
 
 namespace cram {
 namespace ptx {
@@ -49,12 +50,31 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 #endif
   return ok != 0;
 }
+// non-blocking probe of a phase
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 // Bounded wait: a protocol bug must surface as a trap (CUDA error), never as a hung GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
+#ifdef CRAM_MBAR_DEBUG  // development builds: say which wait timed out before trapping
+    if (clock64() - t0 > 200000000ll) {
+      printf("mbar timeout: block %d thread %d smem_addr 0x%x parity %u\n", (int)blockIdx.x, (int)threadIdx.x, smem_u32(bar), parity);
+      __trap();
+    }
+#else
     if (clock64() - t0 > 4000000000ll) __trap();  // ~2 s at 2 GHz
+#endif
   }
 }
 
