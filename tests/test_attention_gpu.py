@@ -147,3 +147,52 @@ def test_all_keys_zero_credibility_row_is_defined():
         assert (g[:100, 0] == 0).all() and (g[100:, 0] != 0).any()
         want = ref_attention(q, k, v, cu_of([T], DEV), None, H, Hkv, dh, logcred=lc, head_mask=0b01)
         assert report(f"zero-cred kernel={kern}", got, want) <= 2e-2
+
+
+def test_sm100_persistent_queue_ragged_batches():
+    """The persistent kernel walks a dynamic work queue: many more items than SMs, row blocks past the end of short
+    sequences (never published), stages without tiles, single-row sequences, and the chunked mode (len_q < len_k) --
+    every CTA crosses many item boundaries with TMEM, barriers and rings alive."""
+    rng = np.random.default_rng(3)
+    H, Hkv, dh = 16, 4, 128
+    for trial in range(3):
+        lens = [int(x) for x in rng.integers(1, 900, size=37)] + [1, 128, 129, 256, 257, 1025]
+        rng.shuffle(lens)
+        q, k, v, _ = make_qkv(sum(lens), H, Hkv, dh, torch.bfloat16, DEV, seed=70 + trial)
+        cu = cu_of(lens, DEV)
+        lc = make_logcred(lens, DEV, torch.bfloat16, seed=80 + trial)
+        mask = 0b1010011001011101
+        got = ops.attn_prefill(q, k, v, cu, max(lens), H, Hkv, dh, logcred=lc, head_mask=mask, kernel=SM100)
+        want = ref_attention(q, k, v, cu, None, H, Hkv, dh, logcred=lc, head_mask=mask)
+        assert not torch.isnan(got).any()
+        assert report(f"persistent ragged trial {trial} ({len(lens)} sequences)", got, want) <= 2e-2
+        again = ops.attn_prefill(q, k, v, cu, max(lens), H, Hkv, dh, logcred=lc, head_mask=mask, kernel=SM100)
+        assert torch.equal(got, again)  # the queue hands items to different CTAs from run to run; the bits do not move
+    # chunked: queries are the tail of the keys, many sequences
+    lens_k = [int(x) for x in rng.integers(300, 1500, size=24)]
+    lens_q = [int(min(lk, x)) for lk, x in zip(lens_k, rng.integers(1, 400, size=24))]
+    qf, _, _, _ = make_qkv(sum(lens_q), H, Hkv, dh, torch.bfloat16, DEV, seed=91)
+    _, k, v, _ = make_qkv(sum(lens_k), H, Hkv, dh, torch.bfloat16, DEV, seed=92)
+    lc = make_logcred(lens_k, DEV, torch.bfloat16, seed=93)
+    cuq, cuk = cu_of(lens_q, DEV), cu_of(lens_k, DEV)
+    got = ops.attn_prefill(qf, k, v, cuq, max(lens_q), H, Hkv, dh, logcred=lc, head_mask=0xF0F0, cu_seqlens_k=cuk,
+                           max_seqlen_k=max(lens_k), kernel=SM100)
+    want = ref_attention(qf, k, v, cuq, cuk, H, Hkv, dh, logcred=lc, head_mask=0xF0F0)
+    assert report("persistent chunked", got, want) <= 2e-2
+
+
+def test_sm100_rows_that_see_no_key_give_zero():
+    """len_k < len_q under the causal alignment: the first len_q - len_k query rows see no key at all. They are work
+    items without tiles (the softmax warps write zeros, LSE = -inf), next to items that do have tiles."""
+    H, Hkv, dh = 4, 2, 128
+    lens_q, lens_k = [300, 40, 513], [100, 40, 200]
+    q, _, _, _ = make_qkv(sum(lens_q), H, Hkv, dh, torch.bfloat16, DEV, seed=95)
+    _, k, v, _ = make_qkv(sum(lens_k), H, Hkv, dh, torch.bfloat16, DEV, seed=96)
+    cuq, cuk = cu_of(lens_q, DEV), cu_of(lens_k, DEV)
+    for kern in (GENERIC, SM100):
+        got, lse = ops.attn_prefill(q, k, v, cuq, max(lens_q), H, Hkv, dh, cu_seqlens_k=cuk, max_seqlen_k=max(lens_k),
+                                    kernel=kern, return_lse=True)
+        want = ref_attention(q, k, v, cuq, cuk, H, Hkv, dh)
+        assert not torch.isnan(got).any()
+        assert report(f"no-key rows kernel={kern}", got, want) <= 2e-2
+        assert (got[:200] == 0).all() and torch.isinf(lse[:, :200]).all()  # rows 0..199 of sequence 0 see nothing
