@@ -31,6 +31,7 @@
 // Lazy O rescale (only when a row's max grows by more than 2^8) keeps the correction off the hot loop, and lets the
 // exponentials of a tile be issued speculatively against the standing reference max, in the pass that forms the scores.
 #include <atomic>
+#include <cstdlib>
 #include <mutex>
 #include <type_traits>
 #include <utility>
@@ -77,7 +78,16 @@ __device__ int g_trace_tile;
   } while (0)
 #endif
 
-__device__ unsigned g_work_counter[256];  // dynamic work queues of the persistent kernel, one per launch in flight
+// Per-launch scratch of the persistent kernel, out of a ring of module globals (one entry per launch in flight): the
+// dynamic work-queue counter, and the live-tile masks of the dead-tile pre-pass (bit j of live[seq]: the 128-key tile j
+// of that sequence holds at least one key whose credibility is not zero).
+constexpr int kMaxMaskSeqs = 1024;
+constexpr int kMaxMaskTiles = 64;
+struct LaunchScratch {
+  unsigned counter, pad;
+  unsigned long long live[kMaxMaskSeqs];
+};
+__device__ LaunchScratch g_scratch[64];
 
 struct Barriers {
   uint64_t q_full[2];
@@ -389,9 +399,30 @@ __device__ __forceinline__ void issue_pv_steps(uint32_t o_tmem, uint32_t p_tmem,
 struct alignas(16) Item {
   int idx;  // position in the work list; >= n_items marks the end of the list
   int head, kv_head, seq, pair, q0, len_q, k0, len_k, diag, nt[2], n_max;
-  int pad[3];
+  // Dead-tile skipping: on a head that carries the bias, a tile whose keys all have zero credibility (log = -inf)
+  // contributes P = 0 to every row -- it is never loaded, multiplied or exponentiated. nt / n_max then count LIVE tiles
+  // and the roles walk them through LiveTiles (virtual index v -> key tile j); dense = 1: every tile is live, v == j.
+  unsigned live_lo, live_hi;
+  int dense;
 };
 static_assert(sizeof(Item) == 64, "one scheduler-ring slot");
+
+struct LiveTiles {
+  unsigned long long m;
+  int v;
+  bool dense;
+  __device__ __forceinline__ explicit LiveTiles(const Item& w)
+      : m(((unsigned long long)w.live_hi << 32) | w.live_lo), v(0), dense(w.dense != 0) {}
+  // key tile of the next live tile (callers stop after nt / n_max calls)
+  __device__ __forceinline__ int next() {
+    if (dense) return v++;
+    const int j = __ffsll((long long)m) - 1;
+    m &= m - 1;
+    ++v;
+    return j;
+  }
+};
+__device__ __forceinline__ unsigned long long low_bits(int n) { return n >= 64 ? ~0ull : ((1ull << n) - 1ull); }
 
 __device__ __forceinline__ Item decode_item(const cram_attn_prefill_params& p, const int num_pairs, const int idx) {
   Item w;
@@ -415,7 +446,30 @@ __device__ __forceinline__ Item decode_item(const cram_attn_prefill_params& p, c
     w.nt[s] = (mt * kBlockM < w.len_q && kv_end > 0) ? (kv_end + kBlockN - 1) / kBlockN : 0;
   }
   w.n_max = max(w.nt[0], w.nt[1]);
+  w.live_lo = w.live_hi = 0u;
+  w.dense = 1;
   return w;
+}
+
+// Pre-pass of dead-tile skipping: one warp per (sequence, 128-key tile) ORs the tile's bit into live[seq] when any of its
+// keys is unbiased (>= bias_len) or has a log-credibility above -inf. 2 bytes per key read once per launch, against the
+// K / V tile loads, MMAs and exponentials of every biased (head, row block) that would have visited a dead tile.
+__global__ void live_tiles_kernel(const cram_attn_prefill_params p, unsigned long long* __restrict__ live) {
+  const int tiles = (p.max_seqlen_k + kBlockN - 1) / kBlockN;
+  const int wid = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  const int seq = wid / tiles, j = wid % tiles;
+  if (seq >= p.n_seq) return;
+  const int32_t* cuk = p.cu_seqlens_k ? p.cu_seqlens_k : p.cu_seqlens_q;
+  const int k0 = cuk[seq], len_k = cuk[seq + 1] - k0;
+  if (j * kBlockN >= len_k) return;
+  const int bias_len = p.bias_len ? p.bias_len[seq] : len_k;
+  bool any = false;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const int key = j * kBlockN + lane * 4 + e;
+    if (key < len_k) any |= key >= bias_len || !(load_logcred(p.logcred, (int64_t)k0 + key, p.logcred_dtype) == -INFINITY);
+  }
+  if (__any_sync(0xffffffffu, any) && lane == 0) atomicOr(&live[seq], 1ull << j);
 }
 
 // PERSISTENT kernel: one CTA per SM walks a dynamic queue of work items (atomic counter; the first item of a CTA is its
@@ -427,7 +481,8 @@ template <typename T, int DH>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                           const __grid_constant__ CUtensorMap tmap_v, const cram_attn_prefill_params p,
-                          const int num_pairs, const int n_items, unsigned* __restrict__ work_counter) {
+                          const int num_pairs, const int n_items, unsigned* __restrict__ work_counter,
+                          const unsigned long long* __restrict__ live_masks, const int mask_tiles) {
   using S = Smem<DH>;
   constexpr int kSlabs = DH / 64;
   constexpr uint32_t kAbFmt = DType<T>::code == CRAM_BF16 ? 1u : 0u;
@@ -534,8 +589,21 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             e.idx = n_items;
             return e;
           }
-          const Item w = decode_item(p, num_pairs, i);
-          if (w.pair * kStages * kBlockM < w.len_q) return w;
+          Item w = decode_item(p, num_pairs, i);
+          if (w.pair * kStages * kBlockM >= w.len_q) continue;
+          // (a sequence longer than the caller's max_seqlen_k has tiles the pre-pass never looked at: it runs dense)
+          if (w.n_max <= mask_tiles && ((p.head_mask >> w.head) & 1ull)) {
+            const unsigned long long m = live_masks[w.seq] & low_bits(w.n_max);
+            if (m != low_bits(w.n_max)) {
+              w.nt[0] = __popcll(m & low_bits(w.nt[0]));
+              w.nt[1] = __popcll(m & low_bits(w.nt[1]));
+              w.n_max = max(w.nt[0], w.nt[1]);
+              w.live_lo = (unsigned)m;
+              w.live_hi = (unsigned)(m >> 32);
+              w.dense = 0;
+            }
+          }
+          return w;
         }
       };
       // lane 0 runs the queue and the loads; the whole warp only meets at the end
@@ -549,8 +617,10 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
           const Item w_next = take();
           publish(it + 1, w_next);
           if (w.n_max > 0) {  // n_max = 0: rows that see no key at all (len_k < len_q); the softmax warps write zeros
-          auto load_k = [&](int j) {
-            const int g = gt + j, st = g % kKV;
+          LiveTiles lk(w), lv(w);  // K runs two live tiles ahead of V
+          auto load_k = [&](int vt) {
+            const int j = lk.next();
+            const int g = gt + vt, st = g % kKV;
             ptx::mbar_wait(&bar->k_empty[st], ((g / kKV) & 1) ^ 1);
             ptx::mbar_expect_tx(&bar->k_full[st], S::kTileBytes);
 #pragma unroll
@@ -573,15 +643,16 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                                     w.head * DH + sl * 64, w.q0 + (w.pair * kStages + s) * kBlockM, ptx::kL2EvictFirst);
           }
           if (w.n_max > 1) load_k(1);
-          for (int j = 0; j < w.n_max; ++j) {
-            const int g = gt + j, st = g % kKV;
+          for (int vt = 0; vt < w.n_max; ++vt) {
+            const int j = lv.next();
+            const int g = gt + vt, st = g % kKV;
             ptx::mbar_wait(&bar->v_empty[st], ((g / kKV) & 1) ^ 1);
             ptx::mbar_expect_tx(&bar->v_full[st], S::kTileBytes);
 #pragma unroll
             for (int sl = 0; sl < kSlabs; ++sl)
               ptx::tma_load_2d_hint(smem + S::kV + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_v, &bar->v_full[st],
                                     w.kv_head * DH + sl * 64, w.k0 + j * kBlockN, ptx::kL2EvictLast);
-            if (j + 2 < w.n_max) load_k(j + 2);
+            if (vt + 2 < w.n_max) load_k(vt + 2);
           }
           }
           gt += w.n_max;
@@ -602,8 +673,10 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         if (w.idx >= n_items) break;
         const bool biased = p.logcred != nullptr && ((p.head_mask >> w.head) & 1ull);
         const int bias_len = p.bias_len ? p.bias_len[w.seq] : w.len_k;
-        for (int j = 0; j < w.n_max; ++j) {
-          const int g = gt + j;
+        LiveTiles lt(w);
+        for (int vt = 0; vt < w.n_max; ++vt) {
+          const int j = lt.next();
+          const int g = gt + vt;
           if (g >= kKV) ptx::mbar_wait(&bar->v_empty[g % kKV], ((g / kKV) & 1) ^ 1);
           float4 b4;
           float* bp = reinterpret_cast<float*>(&b4);
@@ -666,7 +739,6 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
           if (cur.nt[s] > 0) issue_qk(s, cur, gt, 0);
       }
       while (have) {
-        const bool have_next = fetch(nxt);
         const int gt_next = gt + cur.n_max;
         for (int j = 0; j < cur.n_max; ++j) {
           const int g = gt + j, st = g % kKV;
@@ -694,6 +766,9 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         // last P V of each stage: chaining stage 0's (it finishes a tile earlier in a causal item) put 512 tensor cycles
         // in front of stage 1's last P V + Q K^T, the critical path of the item's end. Measured at 16 x 2048 causal:
         // 802 TFLOP/s chained (blocking on the next Q / K[0]), 841 chained only when both had landed, 896-904 not chained.
+        // (The next item is also only READ here: its entry carries the live-tile mask, a dependent global load of the
+        // producer's, and nothing above needs it.)
+        const bool have_next = fetch(nxt);
         if (have_next) {
 #pragma unroll
           for (int s = 0; s < kStages; ++s)
@@ -734,8 +809,10 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       const int nt = w.nt[s];
       float m_ref = -INFINITY, m_next = -INFINITY, l = 0.f;
 
-      for (int j = 0; j < nt; ++j, ++tc) {
-        const int g = gt + j, bs = g % kBiasRing;
+      LiveTiles lt(w);
+      for (int vt = 0; vt < nt; ++vt, ++tc) {
+        const int j = lt.next();  // key tile (causal geometry); vt = position in this item's stream of live tiles
+        const int g = gt + vt, bs = g % kBiasRing;
         ptx::mbar_wait(&bar->bias_full[bs], (g / kBiasRing) & 1);
         ptx::mbar_wait(&bar->s_full[s], tc & 1);
         ptx::tc_fence_after();
@@ -745,8 +822,9 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
 
         auto tile = [&](auto diag_tag) {
           constexpr bool kDiag = decltype(diag_tag)::value;
-          if (j == 0) {
-            // reference of a fresh row block: the max of its first 32 keys (column 0 is visible to every row)
+          if (vt == 0) {
+            // reference of a fresh row block: the max of its first 32 keys (of the first live tile; a row that sees none of them yet
+            // keeps m_ref = -inf and takes the exact path at its first visible key)
             m_ref = chunks_max<kDiag>(s_base, b_addr, sc2, climit, 0, 1);
             m_next = m_ref;
           } else {
@@ -774,7 +852,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                 ptx::mbar_wait(&bar->o_half[s], tc & 1);
                 ptx::tc_fence_after();
               }
-              if (j > 0 || h == 1) rescale_o<DH>(o_addr, (m_new > m_ref) ? ex2(m_ref - m_new) : 1.0f, l);
+              if (vt > 0 || h == 1) rescale_o<DH>(o_addr, (m_new > m_ref) ? ex2(m_ref - m_new) : 1.0f, l);
               m_ref = m_new;
               m_next = fmaxf(m_next, m_ref);
               l += exact_pass<T, kDiag>(s_base, b_addr, sc2, climit, m_ref, 2 * h, 2 * h + 2);
@@ -889,14 +967,30 @@ int launch_t(const cram_attn_prefill_params& p, cudaStream_t stream) {
     CRAM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<DH>::kRequest));
     attr.flag() = true;
   }
-  // dynamic work queue: one counter per launch out of a ring of 256 module globals, zeroed on the launching stream
+  // per-launch scratch (work-queue counter + live-tile masks) out of a ring of 64 module globals, zeroed on the launching
+  // stream
   static std::atomic<unsigned> launch_seq{0};
-  unsigned* counters = nullptr;
-  CRAM_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&counters), g_work_counter));
-  unsigned* counter = counters + (launch_seq.fetch_add(1) & 255u);
-  CRAM_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned), stream));
+  LaunchScratch* ring = nullptr;
+  CRAM_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ring), g_scratch));
+  LaunchScratch* scratch = ring + (launch_seq.fetch_add(1) & 63u);
+  // Dead-tile skipping needs a bias, a biased head, and a batch that fits the mask layout (<= 1024 sequences of <= 64
+  // tiles = 8192 keys); anything else runs every tile. CRAM_B200_NO_DEAD_TILES=1 turns it off (A/B timing, tests).
+  static const bool skip_off = [] {
+    const char* e = getenv("CRAM_B200_NO_DEAD_TILES");
+    return e != nullptr && e[0] != '\0' && e[0] != '0';
+  }();
+  const int max_tiles = (p.max_seqlen_k + kBlockN - 1) / kBlockN;
+  const bool masks = !skip_off && p.logcred != nullptr && p.head_mask != 0 && p.n_seq <= kMaxMaskSeqs && max_tiles > 0 &&
+                     max_tiles <= kMaxMaskTiles;
+  CRAM_CUDA(cudaMemsetAsync(scratch, 0, masks ? 8 + sizeof(unsigned long long) * p.n_seq : 8, stream));
+  if (masks) {
+    const long long warps = (long long)p.n_seq * max_tiles;
+    live_tiles_kernel<<<(unsigned)((warps + 7) / 8), 256, 0, stream>>>(p, scratch->live);
+    if ((rc = check_launch("live_tiles_kernel")) != CRAM_OK) return rc;
+  }
   const int grid = (int)(n_items < sm_count() ? n_items : sm_count());
-  kern<<<grid, kThreads, Smem<DH>::kRequest, stream>>>(tq, tk, tv, p, num_pairs, (int)n_items, counter);
+  kern<<<grid, kThreads, Smem<DH>::kRequest, stream>>>(tq, tk, tv, p, num_pairs, (int)n_items, &scratch->counter,
+                                                       scratch->live, masks ? max_tiles : 0);
   return check_launch("attn_prefill_sm100_kernel");
 }
 

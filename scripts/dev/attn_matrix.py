@@ -2,6 +2,7 @@
 cram_b200/_build/libcram_b200_<name>.so (one subprocess per library: CRAM_B200_LIB is read at load time).
     python scripts/dev/attn_matrix.py            # all libraries
     python scripts/dev/attn_matrix.py --one      # (internal) the library in CRAM_B200_LIB
+CRAM_B200_NO_DEAD_TILES=1 in the environment times the same kernel with dead-tile skipping off.
 """
 import glob
 import os
@@ -17,6 +18,9 @@ SHAPES = [  # name, B, T, H, Hkv, causal
     ("c4x8192", 4, 8192, 32, 8, True),
     ("c1x32768", 1, 32768, 32, 8, True),
     ("c64x512", 64, 512, 32, 8, True),
+    # the bench workload's credibility pattern: one zero-credibility document per prompt (keys 20..419 -> tiles 1 and 2
+    # are dead on the 28 biased heads); TF = the FULL causal FLOPs / time, so skipping shows as a higher figure
+    ("z16x2048", 16, 2048, 32, 8, True),
 ]
 
 
@@ -39,6 +43,9 @@ def one():
         cu = cu.to(dev)
         lc = torch.zeros(total, device=dev).bfloat16()
         lc[100:min(900, total)] = -0.69
+        if name.startswith("z"):
+            for b in range(B):
+                lc[int(cu[b]) + 20:int(cu[b]) + 420] = float("-inf")
         flops = 4.0 * dh * H * sum((t * (t + 1) / 2 if causal else t * t) for t in lens)
         reps = 10 if T <= 8192 else 4
         run = lambda: ops.attn_prefill(q, k, v, cu, T, H, Hkv, dh, logcred=lc, head_mask=0x0FFFFFFF, causal=causal, kernel=2)

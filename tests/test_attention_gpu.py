@@ -196,3 +196,76 @@ def test_sm100_rows_that_see_no_key_give_zero():
         assert not torch.isnan(got).any()
         assert report(f"no-key rows kernel={kern}", got, want) <= 2e-2
         assert (got[:200] == 0).all() and torch.isinf(lse[:, :200]).all()  # rows 0..199 of sequence 0 see nothing
+
+
+def _dead_doc_logcred(lens, dead, dtype=torch.bfloat16):
+    """log-credibility 0 everywhere except the listed (sequence, first key, last key + 1) spans, which are -inf."""
+    parts = [torch.zeros(T, dtype=dtype) for T in lens]
+    for s, a, b in dead:
+        parts[s][a:b] = float("-inf")
+    return torch.cat(parts).to(DEV)
+
+
+def test_sm100_dead_tiles_are_skipped_exactly():
+    """Dead-tile skipping (live_tiles_kernel + LiveTiles): 128-key tiles whose keys all have zero credibility are never
+    visited on the biased heads. Spans that cover whole tiles, a dead prefix (row blocks that see no live key at all ->
+    zeros), a sequence that is dead end to end, spans that cover no whole tile, and heads outside the mask, whose
+    output must stay bit-identical to clean attention."""
+    H, Hkv, dh = 8, 2, 128
+    lens = [2048, 1500, 700, 130, 257]
+    dead = [(0, 20, 420), (0, 1024, 1536), (1, 0, 512), (2, 100, 200), (2, 300, 390), (3, 0, 130), (4, 128, 256)]
+    mask = 0b10110101
+    for dtype in (torch.bfloat16, torch.float16):
+        q, k, v, _ = make_qkv(sum(lens), H, Hkv, dh, dtype, DEV, seed=101)
+        cu = cu_of(lens, DEV)
+        lc = _dead_doc_logcred(lens, dead, dtype)
+        got = ops.attn_prefill(q, k, v, cu, max(lens), H, Hkv, dh, logcred=lc, head_mask=mask, kernel=SM100)
+        want = ref_attention(q, k, v, cu, None, H, Hkv, dh, logcred=lc, head_mask=mask)
+        assert not torch.isnan(got).any()
+        assert report(f"dead tiles {dtype}", got, want) <= 2e-2
+        gen = ops.attn_prefill(q, k, v, cu, max(lens), H, Hkv, dh, logcred=lc, head_mask=mask, kernel=GENERIC)
+        assert report(f"dead tiles {dtype} vs generic kernel", got, gen.double()) <= 2e-2
+        clean = ops.attn_prefill(q, k, v, cu, max(lens), H, Hkv, dh, kernel=SM100)
+        g, c = got.view(-1, H, dh), clean.view(-1, H, dh)
+        for h in range(H):
+            if not (mask >> h) & 1:
+                assert torch.equal(g[:, h], c[:, h]), f"head {h} carries no bias and must not move"
+        biased = [h for h in range(H) if (mask >> h) & 1]
+        o1, o3 = int(cu[1]), int(cu[3])
+        assert (g[o1:o1 + 512][:, biased] == 0).all()        # sequence 1: rows 0..511 see only dead keys
+        assert (g[o1 + 512:o1 + 640][:, biased] != 0).any()
+        assert (g[o3:o3 + 130][:, biased] == 0).all()        # sequence 3 is dead end to end
+        again = ops.attn_prefill(q, k, v, cu, max(lens), H, Hkv, dh, logcred=lc, head_mask=mask, kernel=SM100)
+        assert torch.equal(got, again)
+
+
+def test_sm100_dead_tiles_chunked_bias_len_and_long_fallback():
+    """(a) chunked prefill with bias_len: keys >= bias_len carry no bias whatever their log-credibility says, so their
+    tiles are live; (b) a sequence of more than 64 tiles (8192 keys) does not fit the mask layout and runs every tile."""
+    H, Hkv, dh = 4, 2, 128
+    lens_k, lens_q = [1000, 700], [300, 700]
+    q, _, _, _ = make_qkv(sum(lens_q), H, Hkv, dh, torch.bfloat16, DEV, seed=111)
+    _, k, v, _ = make_qkv(sum(lens_k), H, Hkv, dh, torch.bfloat16, DEV, seed=112)
+    lc = torch.full((sum(lens_k),), float("-inf"), dtype=torch.bfloat16, device=DEV)
+    lc[1000 + 384:1000 + 600] = 0
+    bl = torch.tensor([600, 650], dtype=torch.int32, device=DEV)
+    cuq, cuk = cu_of(lens_q, DEV), cu_of(lens_k, DEV)
+    got = ops.attn_prefill(q, k, v, cuq, max(lens_q), H, Hkv, dh, logcred=lc, head_mask=0b0111, cu_seqlens_k=cuk,
+                           max_seqlen_k=max(lens_k), bias_len=bl, kernel=SM100)
+    want = ref_attention(q, k, v, cuq, cuk, H, Hkv, dh, logcred=lc, head_mask=0b0111, bias_len=bl.tolist())
+    assert not torch.isnan(got).any()
+    assert report("dead tiles, chunked + bias_len", got, want) <= 2e-2
+    assert (got.view(-1, H, dh)[300:300 + 384, :3] == 0).all()  # sequence 1, rows 0..383: every visible key is dead
+
+    T, H, Hkv = 65 * 128, 2, 1
+    q, k, v, _ = make_qkv(T, H, Hkv, dh, torch.bfloat16, DEV, seed=113)
+    lc = _dead_doc_logcred([T], [(0, 50, 3000), (0, 5000, 5300)])
+    got = ops.attn_prefill(q, k, v, cu_of([T], DEV), T, H, Hkv, dh, logcred=lc, head_mask=0b01, kernel=SM100)
+    want = ref_attention(q, k, v, cu_of([T], DEV), None, H, Hkv, dh, logcred=lc, head_mask=0b01)
+    assert report("65 tiles: dense fallback", got, want) <= 2e-2
+    T = 64 * 128  # the largest sequence the masks cover
+    q, k, v, _ = make_qkv(T, H, Hkv, dh, torch.bfloat16, DEV, seed=114)
+    lc = _dead_doc_logcred([T], [(0, 50, 3000), (0, 8000, 8192)])
+    got = ops.attn_prefill(q, k, v, cu_of([T], DEV), T, H, Hkv, dh, logcred=lc, head_mask=0b01, kernel=SM100)
+    want = ref_attention(q, k, v, cu_of([T], DEV), None, H, Hkv, dh, logcred=lc, head_mask=0b01)
+    assert report("64 tiles: masks, bit 63", got, want) <= 2e-2
