@@ -68,6 +68,7 @@ SIGNATURES = {
     "cram_attn_prefill": (C.c_int, [C.POINTER(AttnPrefillParams), vp]),
     "cram_attn_decode_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "cram_attn_decode": (C.c_int, [C.POINTER(AttnDecodeParams), vp]),
+    "cram_attn_decode_static": (C.c_int, [C.POINTER(AttnDecodeParams), vp]),
     "cram_kv_append": (C.c_int, [vp, vp, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, vp, vp, vp,
                                  C.c_int64, C.c_int64, C.c_int, vp]),
     "cram_sweep_splice_heads": (C.c_int, [vp, vp, vp, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, vp, vp]),

@@ -4,6 +4,8 @@
 // once per group, 16-byte cp.async into shared memory, warp-shuffle dot-product reductions.
 // The credibility bias is indexed by absolute key position and only applies to keys < bias_len
 // (the prompt), as the reference's hook slices [..., :weight_len] (utils/re_weighting.py:57).
+#include <mutex>
+
 #include "common.cuh"
 
 namespace cram {
@@ -300,4 +302,62 @@ extern "C" int cram_attn_decode(const cram_attn_decode_params* pp, cram_stream_t
     case CRAM_BF16: return launch_decode_t<__nv_bfloat16>(p, n_splits, st);
     default: set_error("cram_attn_decode: bad dtype %d", p.dtype); return CRAM_ERR_INVALID;
   }
+}
+
+// ---- allocation-free variant -------------------------------------------------------------------------------------
+// cram_attn_decode_static: cram_attn_decode for callers that may not allocate (CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc). The split-KV partials (n_seq x n_heads x n_splits x (head_dim + 2) floats) go into
+// a file-scope device array instead of a caller workspace. Every GPU that loads the library holds the array until the
+// process exits; every call on a device shares it, so calls that overlap on the GPU (different streams) race -- run
+// them on one stream. The kernels write every partial the combine kernel reads, so nothing has to start at zero and the
+// previous call's contents are simply overwritten.
+namespace cram {
+namespace {
+constexpr size_t kStaticScratchBytes = (size_t)CRAM_ATTN_DECODE_STATIC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_decode_static_scratch[kStaticScratchBytes];
+
+// The array's name is a host-side stand-in in host code: the device address comes from cudaGetSymbolAddress, asked
+// once per device with that device current.
+int decode_static_scratch(void** out) {
+  static void* ptrs[64] = {};
+  static std::mutex mu;
+  int dev = 0;
+  CRAM_CUDA(cudaGetDevice(&dev));
+  CRAM_REQUIRE(dev >= 0 && dev < 64, "cram_attn_decode_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void* ptr = nullptr;
+    CRAM_CUDA(cudaGetSymbolAddress((void**)&ptr, g_decode_static_scratch));
+    CRAM_REQUIRE(ptr != nullptr, "cram_attn_decode_static: cudaGetSymbolAddress returned a null address");
+    ptrs[dev] = ptr;
+  }
+  *out = ptrs[dev];
+  return CRAM_OK;
+}
+}  // namespace
+}  // namespace cram
+
+extern "C" int cram_attn_decode_static(const cram_attn_decode_params* pp, cram_stream_t stream) {
+  CRAM_REQUIRE(pp != nullptr, "cram_attn_decode_static: null params");
+  cram_attn_decode_params p = *pp;
+  CRAM_REQUIRE(p.n_seq >= 0 && p.n_heads > 0 && p.n_kv_heads > 0 && p.n_heads % p.n_kv_heads == 0 && p.n_heads <= 64,
+               "cram_attn_decode_static: bad head counts (%d / %d)", p.n_heads, p.n_kv_heads);
+  CRAM_REQUIRE(p.page_size > 0 && p.max_seqlen >= 0 && p.head_dim > 0, "cram_attn_decode_static: bad page_size / max_seqlen / head_dim");
+  if (p.n_seq == 0) return CRAM_OK;
+  // fix the split count here (the same choice cram_attn_decode makes) so that the size check is about the launch that runs
+  if (p.n_splits <= 0)
+    p.n_splits = attn_decode_mma_supported(p) ? attn_decode_mma_splits(p) : choose_splits(p.n_seq, p.n_kv_heads, p.max_seqlen);
+  const size_t need = p.n_splits > 1 ? (size_t)p.n_seq * p.n_heads * p.n_splits * (p.head_dim + 2) * sizeof(float) : 0;
+  if (need > kStaticScratchBytes) {
+    set_error("cram_attn_decode_static: %zu bytes of split-KV scratch needed (%d sequences x %d heads x %d splits), the static "
+              "array holds %zu: pass a smaller n_splits / batch, or use cram_attn_decode with a caller workspace",
+              need, p.n_seq, p.n_heads, p.n_splits, kStaticScratchBytes);
+    return CRAM_ERR_WORKSPACE;
+  }
+  void* scratch = nullptr;
+  const int rc = decode_static_scratch(&scratch);
+  if (rc != CRAM_OK) return rc;
+  p.workspace = scratch;
+  p.workspace_bytes = kStaticScratchBytes;
+  return cram_attn_decode(&p, stream);
 }

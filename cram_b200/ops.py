@@ -187,6 +187,40 @@ def attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, b
     return out
 
 
+def attn_decode_static(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_table: torch.Tensor,
+                       seqlens: torch.Tensor, max_seqlen: int, n_heads: int, n_kv_heads: int, head_dim: int, out: torch.Tensor,
+                       scale: Optional[float] = None, logcred: Optional[torch.Tensor] = None, head_mask: int = 0,
+                       bias_len: Optional[torch.Tensor] = None, n_splits: int = 0) -> torch.Tensor:
+    """``attn_decode`` through cram_attn_decode_static: nothing is allocated, here or in the library -- ``out`` is the
+    caller's, the split-KV partials live in the library's static device array (32 MiB; a launch that needs more raises
+    CramError). No counterpart in the reference (include/cram_b200.h). Calls on different streams race on the array."""
+    global launch_count
+    lib = _lib.load()
+    _cuda(q, "q")
+    p = AttnDecodeParams()
+    p.q, p.out = _ptr(q), _ptr(out)
+    p.q_row_stride, p.out_row_stride = q.stride(0), out.stride(0)
+    p.k_cache, p.v_cache = _ptr(k_cache), _ptr(v_cache)
+    p.page_stride, p.token_stride = k_cache.stride(0), k_cache.stride(1)
+    p.block_table, p.block_table_stride = _ptr(block_table), block_table.stride(0)
+    p.seqlens = _ptr(seqlens)
+    p.n_seq, p.page_size, p.max_seqlen = q.shape[0], k_cache.shape[1], int(max_seqlen)
+    p.n_heads, p.n_kv_heads, p.head_dim = n_heads, n_kv_heads, head_dim
+    p.dtype = dtype_code(q.dtype)
+    p.scale = float(scale if scale is not None else head_dim ** -0.5)
+    if logcred is not None and head_mask:
+        p.logcred, p.logcred_stride, p.logcred_dtype = _ptr(logcred), logcred.stride(0), dtype_code(logcred.dtype)
+    else:
+        p.logcred, p.logcred_stride, p.logcred_dtype = None, 0, CRAM_F32
+    p.head_mask = int(head_mask) & 0xFFFFFFFFFFFFFFFF
+    p.bias_len = _ptr(bias_len)
+    p.n_splits = n_splits
+    p.workspace, p.workspace_bytes = None, 0
+    check(lib.cram_attn_decode_static(C.byref(p), _stream()), "cram_attn_decode_static")
+    launch_count += 2
+    return out
+
+
 def kv_append(k: torch.Tensor, v: torch.Tensor, slot_mapping: torch.Tensor, k_cache: torch.Tensor,
               v_cache: torch.Tensor, n_kv_heads: int, head_dim: int) -> None:
     global launch_count

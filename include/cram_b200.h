@@ -137,6 +137,19 @@ typedef struct cram_attn_decode_params {
 size_t cram_attn_decode_workspace_bytes(int n_seq, int n_heads, int head_dim, int max_seqlen, int n_splits);
 int cram_attn_decode(const cram_attn_decode_params* p, cram_stream_t stream);
 
+/* Allocation-free variant of cram_attn_decode. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it). Same inputs, outputs and arithmetic as cram_attn_decode; p->workspace / p->workspace_bytes are ignored and
+ * the split-KV partials go into a static device array of CRAM_ATTN_DECODE_STATIC_SCRATCH_BYTES inside the library (every
+ * GPU that loads the library holds it until the process exits). It calls no cudaMalloc / cudaFree / allocating routine.
+ * A launch that needs more (n_seq * n_heads * n_splits * (head_dim + 2) * 4 bytes, n_splits as given or as chosen
+ * automatically) is rejected with CRAM_ERR_WORKSPACE and a message in cram_last_error(). All calls on a device share the
+ * array: calls that overlap on the GPU (different streams, no ordering between them) race -- keep them on one stream.
+ * The array keeps the previous call's contents; the kernels overwrite every partial they later read, nothing needs
+ * clearing. */
+#define CRAM_ATTN_DECODE_STATIC_SCRATCH_BYTES (32u << 20)
+int cram_attn_decode_static(const cram_attn_decode_params* p, cram_stream_t stream);
+
 /* scatter freshly projected K/V rows into the paged cache: row r goes to slot_mapping[r]
  * (= page*page_size + slot; negative = skip). */
 int cram_kv_append(const void* k, const void* v, int64_t k_row_stride, int64_t v_row_stride,
