@@ -12,6 +12,62 @@ __device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) { uint64_t r; 
 __device__ __forceinline__ float ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ uint32_t pack(float lo, float hi) { uint32_t r; asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo)); return r; }
 
+// volatile twins: the compiler keeps volatile asm statements in program order when it emits PTX (ptxas may still move them)
+__device__ __forceinline__ uint64_t ffma2v(uint64_t a, uint64_t b, uint64_t c) { uint64_t r; asm volatile("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ uint64_t fadd2v(uint64_t a, uint64_t b) { uint64_t r; asm volatile("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ float ex2v(float x) { float y; asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ uint32_t packv(float lo, float hi) { uint32_t r; asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo)); return r; }
+__device__ __forceinline__ uint64_t fmul2(uint64_t a, uint64_t b) { uint64_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+// 2^x for two lanes on the FMA / ALU pipes (no MUFU): clamp to [-127, 128], split into integer n = round(x) and fraction
+// f in [-0.5, 0.5] through the 1.5 * 2^23 (+127) magic add, degree-DEG polynomial in f, times 2^n built by a shift.
+// x <= -127 gives exactly 0, x >= 127.5 gives +inf (the kernel's overflow detector relies on both).
+template <int DEG>
+__device__ __forceinline__ uint64_t ex2_poly2(float x0, float x1) {
+  constexpr float M = 12582912.f + 127.f;
+  x0 = fminf(fmaxf(x0, -127.f), 128.f);
+  x1 = fminf(fmaxf(x1, -127.f), 128.f);
+  const uint64_t xc = pk2(x0, x1);
+  const uint64_t y = fadd2(xc, pk2(M, M));
+  const uint64_t n = fadd2(y, pk2(-M, -M));
+  const uint64_t f = ffma2(n, pk2(-1.f, -1.f), xc);
+  uint64_t p;
+  if (DEG == 3) {
+    p = ffma2(f, pk2(0.055171459913253784f, 0.055171459913253784f), pk2(0.2426108568906784f, 0.2426108568906784f));
+    p = ffma2(p, f, pk2(0.6932609677314758f, 0.6932609677314758f));
+    p = ffma2(p, f, pk2(0.9999281167984009f, 0.9999281167984009f));
+  } else {
+    p = ffma2(f, pk2(0.23842696845531464f, 0.23842696845531464f), pk2(0.703445315361023f, 0.703445315361023f));
+    p = ffma2(p, f, pk2(1.0004431009292603f, 1.0004431009292603f));
+  }
+  float y0, y1;
+  upk2(y, y0, y1);
+  return fmul2(p, pk2(__uint_as_float(__float_as_uint(y0) << 23), __uint_as_float(__float_as_uint(y1) << 23)));
+}
+__global__ void check_poly(float* maxrel) {
+  float worst3 = 0.f, worst2 = 0.f;
+  for (int i = threadIdx.x; i < 4000000; i += blockDim.x) {
+    const float x = -130.f + i * (260.f / 4000000.f);
+    float a, b, c, d;
+    upk2(ex2_poly2<3>(x, x + 0.37f), a, b);
+    upk2(ex2_poly2<2>(x, x + 0.37f), c, d);
+    const float ra = exp2f(x), rb = exp2f(x + 0.37f);
+    if (x > -126.f && x < 127.f) {
+      worst3 = fmaxf(worst3, fabsf(a / ra - 1.f));
+      worst2 = fmaxf(worst2, fabsf(c / ra - 1.f));
+    }
+    if (x + 0.37f > -126.f && x + 0.37f < 127.f) worst3 = fmaxf(worst3, fabsf(b / rb - 1.f));
+    if (x <= -127.5f && (a != 0.f || c != 0.f)) worst3 = 1e9f;
+    if (x >= 128.f && !(a > 3e38f)) worst3 = 2e9f;
+  }
+  float z0, z1, z2, z3;
+  upk2(ex2_poly2<3>(-INFINITY, INFINITY), z0, z1);
+  upk2(ex2_poly2<3>(-1e30f, 1e30f), z2, z3);
+  if (z0 != 0.f || z2 != 0.f || !(z1 > 3e38f) || !(z3 > 3e38f)) worst3 = 3e9f;
+  atomicMax(reinterpret_cast<int*>(maxrel), __float_as_int(worst3));
+  atomicMax(reinterpret_cast<int*>(maxrel) + 1, __float_as_int(worst2));
+}
+
+// MODE 4 / 5 / 6 / 7: the full mix with 1/4, 1/2, 3/4, all of the exponentials on the polynomial (degree 3); 8: 1/2 at degree 2
 // MODE 0: full mix; 1: no MUFU (identity); 2: MUFU + pack only (no FFMA2 / FADD2); 3: full mix + row max (FMNMX3)
 template <int MODE>
 __global__ void k(const float* __restrict__ in, uint32_t* out, long long* cyc, int iters) {
@@ -56,6 +112,12 @@ __global__ void k(const float* __restrict__ in, uint32_t* out, long long* cyc, i
       }
       float p0, p1, p2, p3;
       if (MODE == 1) { p0 = e0; p1 = e1; p2 = e2; p3 = e3; }
+      else if (MODE >= 4) {
+        constexpr int DEG = MODE == 8 ? 2 : 3;
+        const bool pa = MODE == 7 || (MODE == 6 && (i & 4)), pb = MODE == 5 || MODE == 6 || MODE == 7 || MODE == 8 || (MODE == 4 && (i & 4));
+        if (pa) upk2(ex2_poly2<DEG>(e0, e1), p0, p1); else { p0 = ex2(e0); p1 = ex2(e1); }
+        if (pb) upk2(ex2_poly2<DEG>(e2, e3), p2, p3); else { p2 = ex2(e2); p3 = ex2(e3); }
+      }
       else { p0 = ex2(e0); p1 = ex2(e1); p2 = ex2(e2); p3 = ex2(e3); }
       if (MODE != 2) {
         la = fadd2(la, pk2(p0, p1));
@@ -75,11 +137,74 @@ __global__ void k(const float* __restrict__ in, uint32_t* out, long long* cyc, i
   out[blockIdx.x * blockDim.x + threadIdx.x] = acc ^ __float_as_uint(l0 + l1 + l2 + l3 + mx0 + mx1);
   if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
 }
+// MODE 9: the full mix as a hand-interleaved software pipeline over pairs of elements: between two MUFU.EX2 of pair k sit
+// the score FFMA2 + FADD2 of pair k + LEAD and the row-sum FADD2 + pack of pair k - LAG.
+template <int LEAD, int LAG>
+__global__ void kpipe(const float* __restrict__ in, uint32_t* out, long long* cyc, int iters) {
+  __shared__ float bias[128];
+  if (threadIdx.x < 128) bias[threadIdx.x] = in[threadIdx.x] * 0.01f;
+  uint64_t s2[16];
+  for (int i = 0; i < 16; ++i) s2[i] = pk2(in[(threadIdx.x * 32 + 2 * i) & 1023], in[(threadIdx.x * 32 + 2 * i + 1) & 1023]);
+  __syncthreads();
+  const uint64_t sc2 = pk2(0.127f, 0.127f);
+  const uint64_t negm = pk2(-1.5f, -1.5f);
+  uint64_t la = pk2(0.f, 0.f), lb = pk2(0.f, 0.f);
+  uint32_t acc = 0;
+  long long t0 = clock64();
+  for (int it = 0; it < iters; ++it) {
+    const uint64_t* b2 = reinterpret_cast<const uint64_t*>(&bias[32 * (it & 3)]);
+    uint64_t x[16];
+    float p[32];
+    uint32_t pk[16];
+#pragma unroll
+    for (int k = 0; k < LEAD; ++k) x[k] = fadd2v(ffma2v(s2[k], sc2, b2[k]), negm);
+#pragma unroll
+    for (int k = 0; k < 16 + LAG; ++k) {
+      float e0, e1;
+      if (k < 16) {
+        upk2(x[k], e0, e1);
+        p[2 * k] = ex2v(e0);
+      }
+      if (k + LEAD < 16) x[k + LEAD] = fadd2v(ffma2v(s2[k + LEAD], sc2, b2[k + LEAD]), negm);
+      if (k < 16) p[2 * k + 1] = ex2v(e1);
+      if (k >= LAG) {
+        const int j = k - LAG;
+        if (j & 1) lb = fadd2v(lb, pk2(p[2 * j], p[2 * j + 1]));
+        else la = fadd2v(la, pk2(p[2 * j], p[2 * j + 1]));
+        pk[j] = packv(p[2 * j], p[2 * j + 1]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc ^= pk[i];
+    s2[0] = fadd2(s2[0], pk2(1e-3f, 1e-3f));
+  }
+  long long t1 = clock64();
+  float l0, l1, l2, l3;
+  upk2(la, l0, l1);
+  upk2(lb, l2, l3);
+  out[blockIdx.x * blockDim.x + threadIdx.x] = acc ^ __float_as_uint(l0 + l1 + l2 + l3);
+  if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+}
+template <int LEAD, int LAG>
+void run_pipe(const float* in) {
+  uint32_t* out; long long* cyc;
+  cudaMalloc(&out, 148 * 1024 * 4); cudaMalloc(&cyc, 148 * 8);
+  for (int warps : {4, 8}) {
+    int iters = 4000;
+    kpipe<LEAD, LAG><<<148, warps * 32>>>(in, out, cyc, iters);
+    cudaDeviceSynchronize();
+    long long h[148]; cudaMemcpy(h, cyc, sizeof(h), cudaMemcpyDeviceToHost);
+    double per_elem_warp = (double)h[0] / (iters * 32.0);
+    printf("interleaved lead %d lag %d       warps/SMSP=%d  cycles per element: per warp %.2f, per sub-partition %.2f\n", LEAD, LAG, warps / 4,
+           per_elem_warp, per_elem_warp / (warps / 4.0));
+  }
+  cudaFree(out); cudaFree(cyc);
+}
 template <int MODE>
 void run(const char* name, const float* in) {
   uint32_t* out; long long* cyc;
   cudaMalloc(&out, 148 * 1024 * 4); cudaMalloc(&cyc, 148 * 8);
-  for (int warps : {4, 8, 16}) {
+  for (int warps : {4, 8}) {
     int iters = 4000;
     k<MODE><<<148, warps * 32>>>(in, out, cyc, iters);
     cudaDeviceSynchronize();
@@ -94,6 +219,13 @@ int main() {
   float* in; cudaMalloc(&in, 4096); 
   float h[1024]; for (int i = 0; i < 1024; ++i) h[i] = (i % 37) * 0.1f - 1.7f;
   cudaMemcpy(in, h, 4096, cudaMemcpyHostToDevice);
+  float* mr; cudaMalloc(&mr, 8); cudaMemset(mr, 0, 8);
+  check_poly<<<1, 1024>>>(mr);
+  float hm[2]; cudaMemcpy(hm, mr, 8, cudaMemcpyDeviceToHost);
+  printf("ex2_poly2 max relative error on [-126, 127]: degree 3 %.3g, degree 2 %.3g (>= 1e9 = an edge case failed)\n", hm[0], hm[1]);
+  run_pipe<2, 2>(in); run_pipe<3, 3>(in); run_pipe<4, 4>(in); run_pipe<2, 4>(in);
+  run<4>("1/4 polynomial", in); run<5>("1/2 polynomial", in); run<6>("3/4 polynomial", in); run<7>("all polynomial", in);
+  run<8>("1/2 polynomial, degree 2", in);
   run<0>("full mix", in); run<3>("full mix + FMNMX3", in); run<1>("mix without MUFU", in); run<2>("MUFU + F2FP + LDS only", in);
   printf("err=%s\n", cudaGetErrorString(cudaGetLastError()));
 }
