@@ -257,15 +257,50 @@ def test_sm100_dead_tiles_chunked_bias_len_and_long_fallback():
     assert report("dead tiles, chunked + bias_len", got, want) <= 2e-2
     assert (got.view(-1, H, dh)[300:300 + 384, :3] == 0).all()  # sequence 1, rows 0..383: every visible key is dead
 
+    # 65 tiles: beyond the 64-bit live-tile mask of a sequence -- every tile runs (dead spans still give exact zeros)
     T, H, Hkv = 65 * 128, 2, 1
     q, k, v, _ = make_qkv(T, H, Hkv, dh, torch.bfloat16, DEV, seed=113)
-    lc = _dead_doc_logcred([T], [(0, 50, 3000), (0, 5000, 5300)])
+    lc = _dead_doc_logcred([T], [(0, 50, 3000), (0, 5000, 5300), (0, 8190, 8320)])
     got = ops.attn_prefill(q, k, v, cu_of([T], DEV), T, H, Hkv, dh, logcred=lc, head_mask=0b01, kernel=SM100)
     want = ref_attention(q, k, v, cu_of([T], DEV), None, H, Hkv, dh, logcred=lc, head_mask=0b01)
-    assert report("65 tiles: dense fallback", got, want) <= 2e-2
-    T = 64 * 128  # the largest sequence the masks cover
+    assert report("65 tiles: no masks, every tile runs", got, want) <= 2e-2
+    T = 64 * 128  # one full word, bit 63 dead
     q, k, v, _ = make_qkv(T, H, Hkv, dh, torch.bfloat16, DEV, seed=114)
     lc = _dead_doc_logcred([T], [(0, 50, 3000), (0, 8000, 8192)])
     got = ops.attn_prefill(q, k, v, cu_of([T], DEV), T, H, Hkv, dh, logcred=lc, head_mask=0b01, kernel=SM100)
     want = ref_attention(q, k, v, cu_of([T], DEV), None, H, Hkv, dh, logcred=lc, head_mask=0b01)
     assert report("64 tiles: masks, bit 63", got, want) <= 2e-2
+
+
+def test_sm100_dead_tiles_long_sequences_and_mask_layout_limits():
+    """The layouts the live-tile masks do not cover run every tile and must give the same answers: sequences of more than
+    8192 keys (20 000 and 9 000 here, with long dead spans and a dead prefix), and more than 1024 prompts in a batch."""
+    H, Hkv, dh = 2, 1, 128
+    lens = [20000, 9000]
+    q, k, v, _ = make_qkv(sum(lens), H, Hkv, dh, torch.bfloat16, DEV, seed=121)
+    dead = [(0, 300, 2500), (0, 7000, 9500), (0, 8192 + 100, 16384 + 700), (1, 0, 8200)]
+    lc = _dead_doc_logcred(lens, dead)
+    cu = cu_of(lens, DEV)
+    got = ops.attn_prefill(q, k, v, cu, max(lens), H, Hkv, dh, logcred=lc, head_mask=0b10, kernel=SM100)
+    want = ref_attention(q, k, v, cu, None, H, Hkv, dh, logcred=lc, head_mask=0b10)
+    assert not torch.isnan(got).any()
+    assert report("dead spans, 157 + 71 tiles (no masks)", got, want) <= 2e-2
+    clean = ops.attn_prefill(q, k, v, cu, max(lens), H, Hkv, dh, kernel=SM100)
+    assert torch.equal(got.view(-1, H, dh)[:, 0], clean.view(-1, H, dh)[:, 0])  # head 0 carries no bias
+    assert (got.view(-1, H, dh)[20000:20000 + 8200, 1] == 0).all()               # sequence 1: a dead prefix of 8200 keys
+    del q, k, v, got, want, clean
+    torch.cuda.empty_cache()
+
+    rng = np.random.default_rng(5)
+    lens = [int(x) for x in rng.integers(100, 300, size=1025)]
+    q, k, v, _ = make_qkv(sum(lens), H, Hkv, dh, torch.bfloat16, DEV, seed=122)
+    cu = cu_of(lens, DEV)
+    lc = _dead_doc_logcred(lens, [(b, 0, 128) for b in range(0, 1025, 3)])
+    got = ops.attn_prefill(q, k, v, cu, max(lens), H, Hkv, dh, logcred=lc, head_mask=0b11, kernel=SM100)
+    want = ref_attention(q, k, v, cu, None, H, Hkv, dh, logcred=lc, head_mask=0b11)
+    assert report("1025 prompts: no masks, every tile runs", got, want) <= 2e-2
+    lens = lens[:1024]
+    total = sum(lens)
+    got = ops.attn_prefill(q[:total], k[:total], v[:total], cu[:1025], max(lens), H, Hkv, dh, logcred=lc[:total], head_mask=0b11,
+                           kernel=SM100)
+    assert report("1024 prompts: masks", got, want[:total]) <= 2e-2
