@@ -69,7 +69,25 @@ __device__ int g_trace_tile;
     if (blockIdx.x == CRAM_ATTN_TRACE && threadIdx.x == 0 && g_trace_tile >= 16 && g_trace_tile < 32)          \
       g_trace_fine[g_trace_tile - 16][e] = clock64();                                                         \
   } while (0)
+// Event log of the persistent kernel (one CTA): role `slot` appends (clock, tag) pairs; scripts/trace_attn.py prints the
+// timeline. tag = item ordinal of the CTA << 16 | tile << 4 | event kind.
+__device__ long long g_evlog[8][2048][2];
+#define CRAM_EV_DECL int ev_n = 0
+#define CRAM_EV(slot, item, tile, kind)                                                        \
+  do {                                                                                         \
+    if (blockIdx.x == CRAM_ATTN_TRACE && ev_n < 2048) {                                        \
+      g_evlog[slot][ev_n][0] = clock64();                                                      \
+      g_evlog[slot][ev_n][1] = ((long long)(item) << 16) | ((long long)(tile) << 4) | (kind); \
+      ++ev_n;                                                                                  \
+    }                                                                                          \
+  } while (0)
 #else
+#define CRAM_EV_DECL \
+  do {               \
+  } while (0)
+#define CRAM_EV(slot, item, tile, kind) \
+  do {                                  \
+  } while (0)
 #define CRAM_TRACE(slot, j, e) \
   do {                         \
   } while (0)
@@ -554,11 +572,11 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     setmaxnreg_dec<56>();
     if (warp == 8) {
       // ============================== scheduler + producer =======================================
-      // Per item: Q of both stages (once the previous item's last Q K^T of that stage has completed), K[0], K[1], then per
+      // Per item: K[0], Q of both stages (once the previous item's last Q K^T of that stage has completed), K[1], then per
       // tile j: V[j], K[j+2]. gt = running tile count: ring slot gt % kKV, phase gt / kKV. A slot is re-filled as soon as
       // the last MMA that reads it has completed (k_empty / v_empty are tcgen05.commit arrivals).
       int gt = 0, qi[2] = {0, 0};
-      // publish entry `it` of the scheduler ring (lane 0)
+      // publish entry `it` of the scheduler ring
       auto publish = [&](int it, const Item& w) {
         const int slot = it % kSched;
         if (it >= kSched) ptx::mbar_wait(&bar->item_empty[slot], ((it / kSched) & 1) ^ 1);
@@ -608,14 +626,21 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       };
       // lane 0 runs the queue and the loads; the whole warp only meets at the end
       if (lane == 0) {
+        CRAM_EV_DECL;
         Item w = take();
         publish(0, w);
         for (int it = 0; w.idx < n_items; ++it) {
-          // The NEXT item is published before this item's loads are issued: the MMA warp reads one item ahead (it issues
-          // the next item's first Q K^T behind this item's last P V), and this item's loads wait for ring slots that
-          // only the MMA warp frees.
-          const Item w_next = take();
-          publish(it + 1, w_next);
+          CRAM_EV(3, it, 0, 0);
+          // The NEXT item is taken LATE: three tiles before the end of this item's loads (short items: behind their
+          // first loads). Taking costs ~3800 cycles of dependent global latency (a contended atomic, cu_seqlens, the mask
+          // word); there the producer is between two ring-slot waits with a tile of slack, while at the top of the loop
+          // (v5.4) it sat in front of the next item's Q / K[0] at every item boundary (event log:
+          // profiles/r2_attn_evlog.md). It is also the latest point that still has the next item's record and first
+          // loads out before the consumers get there -- and the later an item is claimed from the dynamic queue, the
+          // better the balance at the tail (claiming one more item ahead cost 7 % at 16 x 2048 causal).
+          Item w_next;
+          bool taken = false;
+          const int take_at = max(w.n_max - 3, 0);
           if (w.n_max > 0) {  // n_max = 0: rows that see no key at all (len_k < len_q); the softmax warps write zeros
           LiveTiles lk(w), lv(w);  // K runs two live tiles ahead of V
           auto load_k = [&](int vt) {
@@ -643,6 +668,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                                     w.head * DH + sl * 64, w.q0 + (w.pair * kStages + s) * kBlockM, ptx::kL2EvictFirst);
           }
           if (w.n_max > 1) load_k(1);
+          CRAM_EV(3, it, 0, 2);
           for (int vt = 0; vt < w.n_max; ++vt) {
             const int j = lv.next();
             const int g = gt + vt, st = g % kKV;
@@ -653,8 +679,19 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
               ptx::tma_load_2d_hint(smem + S::kV + st * S::kTileBytes + sl * S::kSlabBytes, &tmap_v, &bar->v_full[st],
                                     w.kv_head * DH + sl * 64, w.k0 + j * kBlockN, ptx::kL2EvictLast);
             if (vt + 2 < w.n_max) load_k(vt + 2);
+            if (vt == take_at) {
+              CRAM_EV(3, it, vt, 1);
+              w_next = take();
+              publish(it + 1, w_next);
+              taken = true;
+            }
           }
           }
+          if (!taken) {
+            w_next = take();
+            publish(it + 1, w_next);
+          }
+          CRAM_EV(3, it, w.n_max, 3);
           gt += w.n_max;
           w = w_next;
         }
@@ -731,6 +768,8 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         if (j == w.nt[s] - 1) ptx::tc_commit(&bar->q_empty[s]);         // last Q K^T that reads this item's Q tile
       };
       Item cur, nxt;
+      CRAM_EV_DECL;
+      int ev_item = 0;
       bool have = fetch(cur);
       int gt = 0;
       if (have) {
@@ -760,6 +799,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             if (s == 1 || j >= cur.nt[1]) ptx::tc_commit(&bar->v_empty[st]);  // last stage to read V[j]
             ++tc[s];
             if (j + 1 < nt) issue_qk(s, cur, gt, j + 1);
+            CRAM_EV(2, ev_item, j, 4 + s);
           }
         }
         // The next item's first Q K^T of both stages goes out HERE, behind the last P V of the whole item, not behind the
@@ -769,17 +809,22 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         // (The next item is also only READ here: its entry carries the live-tile mask, a dependent global load of the
         // producer's, and nothing above needs it.)
         const bool have_next = fetch(nxt);
+        CRAM_EV(2, ev_item, 0, 6);
         if (have_next) {
 #pragma unroll
           for (int s = 0; s < kStages; ++s)
             if (nxt.nt[s] > 0) issue_qk(s, nxt, gt_next, 0);
         }
+        CRAM_EV(2, ev_item, 0, 7);
+#ifdef CRAM_ATTN_TRACE
+        ++ev_item;
+#endif
         gt = gt_next;
         cur = nxt;
         have = have_next;
       }
     }
-    // warp 11 and the other lanes of warp 9 idle: kItemConsumers counts the MMA lane, the bias warp and the eight
+    // warp 11 and the other lanes of warps 8 and 9 idle: kItemConsumers counts the MMA lane, the bias warp and the eight
     // softmax warps
   } else {
     // ============================== softmax / correction / epilogue ================================
@@ -801,9 +846,12 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
       ptx::mbar_arrive(&bar->p_full[s][h]);
     };
 
+    CRAM_EV_DECL;
+    const bool ev_on = (warp & 3) == 0 && lane == 0;
     for (int it = 0;; ++it) {
       const Item w = next_item(it);
       if (w.idx >= n_items) break;
+      if (ev_on) CRAM_EV(s, it, w.nt[s], 8);
       const int mt = w.pair * kStages + s;
       const int qrow = mt * kBlockM + row;          // row inside the sequence
       const int nt = w.nt[s];
@@ -816,6 +864,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         ptx::mbar_wait(&bar->bias_full[bs], (g / kBiasRing) & 1);
         ptx::mbar_wait(&bar->s_full[s], tc & 1);
         ptx::tc_fence_after();
+        if (ev_on) CRAM_EV(s, it, vt, 9);
         const bool diag_tile = p.causal && (j * kBlockN + kBlockN - 1 > mt * kBlockM + w.diag);
         const int climit = qrow + w.diag - j * kBlockN;  // columns <= climit are visible
         const uint32_t b_addr = bias_addr + bs * kBlockN * 4;
@@ -866,6 +915,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         };
         if (diag_tile) tile(std::true_type{});
         else tile(std::false_type{});
+        if (ev_on) CRAM_EV(s, it, vt, 10);
       }
       gt += w.n_max;
 
@@ -876,6 +926,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         ptx::mbar_wait(&bar->o_final[s], ic & 1);  // committed after the last P V of this stage and item
         ++ic;
         ptx::tc_fence_after();
+        if (ev_on) CRAM_EV(s, it, 0, 11);
         const float inv = l > 0.f ? 1.0f / l : 0.f;
 #pragma unroll
         for (int c = 0; c < DH / 32; ++c) {
@@ -901,6 +952,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         for (int c = 0; c < DH; c += 8) *reinterpret_cast<uint4*>(out + c) = make_uint4(0, 0, 0, 0);
         if (p.lse) p.lse[(int64_t)w.head * p.total_q + w.q0 + qrow] = -INFINITY;
       }
+      if (ev_on) CRAM_EV(s, it, 0, 12);
     }
   }
 
@@ -1022,6 +1074,9 @@ int launch_attn_sm100(const cram_attn_prefill_params& p, cudaStream_t stream) {
 #ifdef CRAM_ATTN_TRACE
 extern "C" int cram_debug_read_trace(long long* host_out) {
   return cudaMemcpyFromSymbol(host_out, cram::g_trace, sizeof(cram::g_trace)) == cudaSuccess ? 0 : -1;
+}
+extern "C" int cram_debug_read_evlog(long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, cram::g_evlog, sizeof(cram::g_evlog)) == cudaSuccess ? 0 : -1;
 }
 extern "C" int cram_debug_read_trace_fine(long long* host_out) {
   return cudaMemcpyFromSymbol(host_out, cram::g_trace_fine, sizeof(cram::g_trace_fine)) == cudaSuccess ? 0 : -1;

@@ -39,7 +39,7 @@ def run():
     buf = np.zeros((24, 64, 4), dtype=np.int64)
     lib.cram_debug_read_trace.argtypes = [ctypes.c_void_p]
     assert lib.cram_debug_read_trace(buf.ctypes.data) == 0
-    t0 = buf[buf > 0].min()
+    t0 = buf[buf > 0].min() if (buf > 0).any() else 0  # (the per-tile stamps predate the persistent kernel: usually empty)
     slots = ((0, "softmax stage0 (warp 0)"), (4, "softmax stage1 (warp 4)"), (8, "mma stage0"), (9, "mma stage1"))
     if os.environ.get("TRACE_SLOTS"):
         slots = tuple((int(x), f"slot {x}") for x in os.environ["TRACE_SLOTS"].split(","))
@@ -53,6 +53,49 @@ def run():
             per = (e[0] - prev) if prev is not None else 0
             prev = e[0]
             print(f"  j={j:2d} start={e[0]-t0:7d}  {e[1]-e[0]:6d} {e[2]-e[1]:6d} {e[3]-e[2]:6d} | {per:6d}")
+
+    if hasattr(lib, "cram_debug_read_evlog"):
+        ev = np.zeros((8, 2048, 2), dtype=np.int64)
+        lib.cram_debug_read_evlog.argtypes = [ctypes.c_void_p]
+        assert lib.cram_debug_read_evlog(ev.ctypes.data) == 0
+        names = {0: "P take.start", 1: "P published next", 2: "P first loads issued", 3: "P all loads issued", 4: "M s0 PV+QK issued",
+                 5: "M s1 PV+QK issued", 6: "M next item read", 7: "M next first QK issued", 8: "S item read", 9: "S S(j) seen",
+                 10: "S tile done", 11: "S o_final seen", 12: "S epilogue done"}
+        role = {0: "softmax0", 1: "softmax1", 2: "mma", 3: "producer"}
+        lo, hi = (int(x) for x in os.environ.get("TRACE_ITEMS", "6,9").split(","))
+        rows = []
+        for slot in range(4):
+            for n in range(2048):
+                c, tag = int(ev[slot, n, 0]), int(ev[slot, n, 1])
+                if c == 0:
+                    break
+                rows.append((c, slot, tag >> 16, (tag >> 4) & 0xFFF, tag & 15))
+        rows.sort()
+        sel = [r for r in rows if lo <= r[2] <= hi]
+        if sel:
+            t0 = sel[0][0]
+            print(f"--- event log of the traced CTA, items {lo}..{hi} (cycles from the first event shown)")
+            last = {}
+            for c, slot, item, tile, kind in sel:
+                d = c - last.get(slot, c)
+                last[slot] = c
+                print(f"  {c - t0:8d}  (+{d:6d})  {role[slot]:9s} item {item:3d} tile {tile:3d}  {names.get(kind, kind)}")
+        # per-item summary for softmax1: item read -> first S seen, last tile done -> o_final -> epilogue done -> next item read
+        print("--- per item (softmax stage 1): tiles | read->S0 | tiles phase | last tile->o_final | epilogue | total")
+        cur = {}
+        for c, slot, item, tile, kind in rows:
+            if slot != 1:
+                continue
+            d = cur.setdefault(item, {})
+            if kind == 8: d["read"] = c; d["nt"] = tile
+            if kind == 9 and "s0" not in d: d["s0"] = c
+            if kind == 10: d["last"] = c
+            if kind == 11: d["of"] = c
+            if kind == 12: d["done"] = c
+        for item in sorted(cur):
+            d = cur[item]
+            if all(k in d for k in ("read", "s0", "last", "of", "done")):
+                print(f"  item {item:3d}: {d['nt']:2d} | {d['s0'] - d['read']:6d} | {d['last'] - d['s0']:7d} | {d['of'] - d['last']:6d} | {d['done'] - d['of']:6d} | {d['done'] - d['read']:7d}")
 
     if hasattr(lib, "cram_debug_read_trace_fine"):
         fine = np.zeros((16, 16), dtype=np.int64)
