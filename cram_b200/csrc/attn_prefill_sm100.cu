@@ -275,7 +275,7 @@ __device__ __forceinline__ void score_chunk(const uint32_t (&raw)[32], const uin
 
 // max over the scores of chunks [c0, c1)
 template <bool kDiag>
-__device__ __forceinline__ float chunks_max(const uint32_t s_addr, const uint32_t bias, const uint64_t sc2, const int climit,
+__device__ __noinline__ float chunks_max(const uint32_t s_addr, const uint32_t bias, const uint64_t sc2, const int climit,
                                             const int c0, const int c1) {
   float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll 1
@@ -297,7 +297,7 @@ __device__ __forceinline__ float chunks_max(const uint32_t s_addr, const uint32_
 // exact pass over chunks [c0, c1) against a known reference: P chunk c (16 packed columns) goes straight over S columns
 // [16c, 16c+16), which belong to chunks already consumed. Returns the row sum.
 template <typename T, bool kDiag>
-__device__ __forceinline__ float exact_pass(const uint32_t s_addr, const uint32_t bias, const uint64_t sc2, const int climit,
+__device__ __noinline__ float exact_pass(const uint32_t s_addr, const uint32_t bias, const uint64_t sc2, const int climit,
                                             const float m_ref, const int c0, const int c1) {
   const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
   const uint64_t negm = pk2(-m_use, -m_use);
@@ -331,7 +331,7 @@ __device__ __forceinline__ float exact_pass(const uint32_t s_addr, const uint32_
 
 // O *= f, l *= f (f = 2^(m_old - m_new) per row): the correction step of the online softmax
 template <int DH>
-__device__ __forceinline__ void rescale_o(const uint32_t o_addr, const float f, float& l) {
+__device__ __noinline__ void rescale_o(const uint32_t o_addr, const float f, float& l) {
   const uint64_t f2 = pk2(f, f);
 #pragma unroll 1
   for (int c = 0; c < DH / 32; ++c) {
