@@ -133,10 +133,16 @@ struct Smem {
   static constexpr int kSched = kBias + kBiasRing * kBlockN * 4;  // Item [kSched]: decoded work items, published by the producer
   static constexpr int kBar = kSched + cram::kSched * 64;
   static constexpr int kTmemPtr = kBar + (int)sizeof(Barriers);
-  static constexpr int kEnd = kTmemPtr + 16;
-  // dynamic smem request: + 1024 for manual alignment; padded above half an SM so that exactly one
-  // CTA (and therefore one 512-column TMEM allocation) is resident per SM.
-  static constexpr int kRequest = (kEnd + 1024) > 120 * 1024 ? (kEnd + 1024) : 120 * 1024;
+  // epilogue staging: per softmax warp TWO 32-row x 32-column boxes of the output (2 KB each, 64-byte rows, 64B swizzle)
+  // that TMA stores carry to global memory; a box is rewritten while the store of the other one is still in flight
+  static constexpr int kOutBoxBytes = 32 * 32 * 2;
+  static constexpr int kOut = (kTmemPtr + 16 + 1023) / 1024 * 1024;
+  static constexpr int kEnd = kOut + 8 * 2 * kOutBoxBytes;
+  // Dynamic smem request: this is ALL of the 227 KB a CTA can have at d = 128 (no slack for a manual round-up: the kernel
+  // has no static shared memory, so the dynamic window starts 1024-aligned, and traps if that ever stops being true);
+  // always above half an SM, so exactly one CTA (one 512-column TMEM allocation) is resident per SM.
+  static constexpr int kRequest = kEnd > 120 * 1024 ? kEnd : 120 * 1024;
+  static_assert(kEnd <= 227 * 1024, "shared memory budget");
 };
 
 __device__ __forceinline__ float ex2(float x) {
@@ -498,7 +504,8 @@ __global__ void live_tiles_kernel(const cram_attn_prefill_params p, unsigned lon
 template <typename T, int DH>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
-                          const __grid_constant__ CUtensorMap tmap_v, const cram_attn_prefill_params p,
+                          const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_o,
+                          const cram_attn_prefill_params p,
                           const int num_pairs, const int n_items, unsigned* __restrict__ work_counter,
                           const unsigned long long* __restrict__ live_masks, const int mask_tiles) {
   using S = Smem<DH>;
@@ -507,8 +514,9 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
   constexpr uint32_t kIdescQK = ptx::umma_idesc_f16(kAbFmt, kBlockM, kBlockN, 0);
   constexpr uint32_t kIdescPV = ptx::umma_idesc_f16(kAbFmt, kBlockM, DH, 1);
 
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((ptx::smem_u32(smem) & 1023u) != 0u) __trap();  // the 128B-swizzled TMA tiles need a 1024-byte aligned base
   Barriers* bar = reinterpret_cast<Barriers*>(smem + S::kBar);
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + S::kTmemPtr);
   float* s_bias = reinterpret_cast<float*>(smem + S::kBias);
@@ -529,6 +537,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     ptx::prefetch_tmap(&tmap_q);
     ptx::prefetch_tmap(&tmap_k);
     ptx::prefetch_tmap(&tmap_v);
+    ptx::prefetch_tmap(&tmap_o);
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&bar->q_full[i], 1);
       ptx::mbar_init(&bar->q_empty[i], 1);
@@ -928,6 +937,46 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         ptx::tc_fence_after();
         if (ev_on) CRAM_EV(s, it, 0, 11);
         const float inv = l > 0.f ? 1.0f / l : 0.f;
+        // Full 32-row slices (every warp except at the ragged end of a sequence) leave through shared memory and a TMA
+        // store: one thread per row writing 16 bytes at a time straight to global memory is 32 separate 128-byte lines
+        // per store instruction -- 2048 L1 wavefronts per stage and item, 2200-3100 cycles in the event log, in the LSU
+        // path the other stage's bias loads need. Staged, it is 64 conflict-free shared-memory wavefronts per warp and
+        // the copy engine does the rest while the warp goes on.
+        const int slice_row0 = mt * kBlockM + (warp & 3) * 32;
+        if (slice_row0 + 32 <= w.len_q) {
+          uint8_t* boxes = smem + S::kOut + warp * 2 * S::kOutBoxBytes;
+#pragma unroll
+          for (int c = 0; c < DH / 32; ++c) {
+            uint8_t* box = boxes + (c & 1) * S::kOutBoxBytes;
+            const uint32_t box_row = ptx::smem_u32(box) + lane * 64;
+            uint32_t o[32];
+            ptx::tmem_ld32(o_addr + c * 32, o);
+            ptx::tc_wait_ld();
+            uint4 v[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              v[i].x = pack2<T>(__uint_as_float(o[8 * i + 0]) * inv, __uint_as_float(o[8 * i + 1]) * inv);
+              v[i].y = pack2<T>(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv);
+              v[i].z = pack2<T>(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv);
+              v[i].w = pack2<T>(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv);
+            }
+            // this box is free once the store BEFORE the previous one has finished reading it (DH / 32 is even: the boxes
+            // alternate across items as well); the issuing lane knows
+            if (lane == 0) ptx::tma_store_wait_read<1>();
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 4; ++i)  // 64B swizzle: 16-byte chunk index ^= (row >> 1) & 3
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(box_row + ((i ^ ((lane >> 1) & 3)) << 4)), "r"(v[i].x),
+                           "r"(v[i].y), "r"(v[i].z), "r"(v[i].w)
+                           : "memory");
+            ptx::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              ptx::tma_store_2d(&tmap_o, box, w.head * DH + c * 32, w.q0 + slice_row0);
+              ptx::tma_store_commit();
+            }
+          }
+        } else {
 #pragma unroll
         for (int c = 0; c < DH / 32; ++c) {
           uint32_t o[32];
@@ -945,6 +994,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             }
           }
         }
+        }
         if (p.lse && row_ok)
           p.lse[(int64_t)w.head * p.total_q + w.q0 + qrow] = l > 0.f ? (m_ref + log2f(l)) * 0.6931471805599453f : -INFINITY;
       } else if (row_ok) {
@@ -956,6 +1006,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     }
   }
 
+  if (warp < 8 && lane == 0) ptx::tma_store_wait<0>();  // this lane's output boxes have reached global memory
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 9) ptx::tmem_dealloc(tmem_base, kTmemCols);
@@ -981,7 +1032,7 @@ EncodeTiledFn get_encode_fn() {
 
 // rows x cols view of packed token rows; box = box_rows rows x 64 elements, 128-byte swizzle.
 int make_tmap(CUtensorMap* m, const void* base, int dtype, int64_t cols, int64_t rows, int64_t row_stride_elems,
-              int box_rows) {
+              int box_rows, int box_cols = 64, CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled not available from the driver");
@@ -989,11 +1040,11 @@ int make_tmap(CUtensorMap* m, const void* base, int dtype, int64_t cols, int64_t
   }
   cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t gstride[1] = {(cuuint64_t)row_stride_elems * 2};
-  cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(m, dtype == CRAM_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
                   const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed with CUresult %d (base %p cols %lld rows %lld stride %lld)", (int)r, base,
               (long long)cols, (long long)rows, (long long)row_stride_elems);
@@ -1004,11 +1055,14 @@ int make_tmap(CUtensorMap* m, const void* base, int dtype, int64_t cols, int64_t
 
 template <typename T, int DH>
 int launch_t(const cram_attn_prefill_params& p, cudaStream_t stream) {
-  CUtensorMap tq, tk, tv;
+  CUtensorMap tq, tk, tv, to;
   int rc;
   if ((rc = make_tmap(&tq, p.q, p.dtype, (int64_t)p.n_heads * DH, p.total_q, p.q_row_stride, kBlockM)) != CRAM_OK) return rc;
   if ((rc = make_tmap(&tk, p.k, p.dtype, (int64_t)p.n_kv_heads * DH, p.total_k, p.k_row_stride, kBlockN)) != CRAM_OK) return rc;
   if ((rc = make_tmap(&tv, p.v, p.dtype, (int64_t)p.n_kv_heads * DH, p.total_k, p.v_row_stride, kBlockN)) != CRAM_OK) return rc;
+  if ((rc = make_tmap(&to, p.out, p.dtype, (int64_t)p.n_heads * DH, p.total_q, p.out_row_stride, 32, 32,
+                      CU_TENSOR_MAP_SWIZZLE_64B)) != CRAM_OK)
+    return rc;
   const int num_pairs = (p.max_seqlen_q + kStages * kBlockM - 1) / (kStages * kBlockM);
   const long long n_items = (long long)num_pairs * p.n_seq * p.n_heads;
   if (n_items == 0) return CRAM_OK;
@@ -1041,7 +1095,7 @@ int launch_t(const cram_attn_prefill_params& p, cudaStream_t stream) {
     if ((rc = check_launch("live_tiles_kernel")) != CRAM_OK) return rc;
   }
   const int grid = (int)(n_items < sm_count() ? n_items : sm_count());
-  kern<<<grid, kThreads, Smem<DH>::kRequest, stream>>>(tq, tk, tv, p, num_pairs, (int)n_items, &scratch->counter,
+  kern<<<grid, kThreads, Smem<DH>::kRequest, stream>>>(tq, tk, tv, to, p, num_pairs, (int)n_items, &scratch->counter,
                                                        scratch->live, masks ? max_tiles : 0);
   return check_launch("attn_prefill_sm100_kernel");
 }

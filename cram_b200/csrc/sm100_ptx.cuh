@@ -108,6 +108,25 @@ __device__ __forceinline__ void tma_load_2d_hint(void* smem_dst, const CUtensorM
       : "memory");
 }
 
+// TMA store of a 2-D box from shared memory (bulk async-group completion): the writers' generic-proxy stores to shared
+// memory must be fenced into the async proxy (fence_proxy_async, every writing lane, before the warp / CTA sync that
+// precedes the issue); the source buffer may be rewritten once tma_store_wait_read<0>() has returned in the issuing lane.
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(m), "r"(smem_u32(smem_src)),
+               "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void tma_store_wait() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+
 // one lane of the (converged) warp; ptxas treats code under this predicate as single-lane, so operands of
 // tcgen05.mma / commit become plain uniform registers instead of a waterfall loop
 __device__ __forceinline__ bool elect_one_sync() {
