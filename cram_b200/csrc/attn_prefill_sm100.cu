@@ -945,13 +945,16 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         const int slice_row0 = mt * kBlockM + (warp & 3) * 32;
         if (slice_row0 + 32 <= w.len_q) {
           uint8_t* boxes = smem + S::kOut + warp * 2 * S::kOutBoxBytes;
+          uint32_t o2[2][32];  // the TMEM load of the next 32 columns is in flight while these are scaled, packed and staged
+          ptx::tmem_ld32(o_addr, o2[0]);
 #pragma unroll
           for (int c = 0; c < DH / 32; ++c) {
             uint8_t* box = boxes + (c & 1) * S::kOutBoxBytes;
             const uint32_t box_row = ptx::smem_u32(box) + lane * 64;
-            uint32_t o[32];
-            ptx::tmem_ld32(o_addr + c * 32, o);
-            ptx::tc_wait_ld();
+            uint32_t(&o)[32] = o2[c & 1];
+            ptx::tc_wait_ld_regs(o);
+            if (c + 1 < DH / 32) ptx::tmem_ld32(o_addr + (c + 1) * 32, o2[(c + 1) & 1]);
+            if (ev_on) CRAM_EV(s, it, c, 13);
             uint4 v[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
@@ -964,6 +967,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             // alternate across items as well); the issuing lane knows
             if (lane == 0) ptx::tma_store_wait_read<1>();
             __syncwarp();
+            if (ev_on) CRAM_EV(s, it, c, 14);
 #pragma unroll
             for (int i = 0; i < 4; ++i)  // 64B swizzle: 16-byte chunk index ^= (row >> 1) & 3
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(box_row + ((i ^ ((lane >> 1) & 3)) << 4)), "r"(v[i].x),

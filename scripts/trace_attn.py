@@ -60,7 +60,8 @@ def run():
         assert lib.cram_debug_read_evlog(ev.ctypes.data) == 0
         names = {0: "P take.start", 1: "P published next", 2: "P first loads issued", 3: "P all loads issued", 4: "M s0 PV+QK issued",
                  5: "M s1 PV+QK issued", 6: "M next item read", 7: "M next first QK issued", 8: "S item read", 9: "S S(j) seen",
-                 10: "S tile done", 11: "S o_final seen", 12: "S epilogue done"}
+                 10: "S tile done", 11: "S o_final seen", 12: "S epilogue done", 13: "S epilogue: O chunk in registers",
+                 14: "S epilogue: box free"}
         role = {0: "softmax0", 1: "softmax1", 2: "mma", 3: "producer"}
         lo, hi = (int(x) for x in os.environ.get("TRACE_ITEMS", "6,9").split(","))
         rows = []
