@@ -133,8 +133,8 @@ struct Smem {
   static constexpr int kSched = kBias + kBiasRing * kBlockN * 4;  // Item [kSched]: decoded work items, published by the producer
   static constexpr int kBar = kSched + cram::kSched * 64;
   static constexpr int kTmemPtr = kBar + (int)sizeof(Barriers);
-  // epilogue staging: per softmax warp TWO 32-row x 32-column boxes of the output (2 KB each, 64-byte rows, 64B swizzle)
-  // that TMA stores carry to global memory; a box is rewritten while the store of the other one is still in flight
+  // epilogue staging: per softmax warp one 32-row x 64-column box of the output (4 KB = 2 x kOutBoxBytes, 128-byte rows,
+  // 128B swizzle) that a TMA store carries to global memory
   static constexpr int kOutBoxBytes = 32 * 32 * 2;
   static constexpr int kOut = (kTmemPtr + 16 + 1023) / 1024 * 1024;
   static constexpr int kEnd = kOut + 8 * 2 * kOutBoxBytes;
@@ -941,42 +941,48 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         // store: one thread per row writing 16 bytes at a time straight to global memory is 32 separate 128-byte lines
         // per store instruction -- 2048 L1 wavefronts per stage and item, 2200-3100 cycles in the event log, in the LSU
         // path the other stage's bias loads need. Staged, it is 64 conflict-free shared-memory wavefronts per warp and
-        // the copy engine does the rest while the warp goes on.
+        // the copy engine does the rest while the warp goes on. (Boxes of 32 columns, double-buffered, measured the same.)
         const int slice_row0 = mt * kBlockM + (warp & 3) * 32;
         if (slice_row0 + 32 <= w.len_q) {
-          uint8_t* boxes = smem + S::kOut + warp * 2 * S::kOutBoxBytes;
-          uint32_t o2[2][32];  // the TMEM load of the next 32 columns is in flight while these are scaled, packed and staged
-          ptx::tmem_ld32(o_addr, o2[0]);
+          // rounds of 64 columns: one 4 KB box per warp (32 rows x 128 bytes, 128B swizzle), one TMA store per round; the
+          // TMEM loads of the next round are in flight while this one is scaled, packed and staged
+          uint8_t* box = smem + S::kOut + warp * 2 * S::kOutBoxBytes;
+          const uint32_t box_row = ptx::smem_u32(box) + lane * 128;
+          uint32_t o2[2][2][32];
+          ptx::tmem_ld32(o_addr, o2[0][0]);
+          ptx::tmem_ld32(o_addr + 32, o2[0][1]);
 #pragma unroll
-          for (int c = 0; c < DH / 32; ++c) {
-            uint8_t* box = boxes + (c & 1) * S::kOutBoxBytes;
-            const uint32_t box_row = ptx::smem_u32(box) + lane * 64;
-            uint32_t(&o)[32] = o2[c & 1];
-            ptx::tc_wait_ld_regs(o);
-            if (c + 1 < DH / 32) ptx::tmem_ld32(o_addr + (c + 1) * 32, o2[(c + 1) & 1]);
-            if (ev_on) CRAM_EV(s, it, c, 13);
-            uint4 v[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              v[i].x = pack2<T>(__uint_as_float(o[8 * i + 0]) * inv, __uint_as_float(o[8 * i + 1]) * inv);
-              v[i].y = pack2<T>(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv);
-              v[i].z = pack2<T>(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv);
-              v[i].w = pack2<T>(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv);
+          for (int r = 0; r < DH / 64; ++r) {
+            ptx::tc_wait_ld_regs(o2[r & 1][0]);
+            ptx::tc_wait_ld_regs(o2[r & 1][1]);
+            if (r + 1 < DH / 64) {
+              ptx::tmem_ld32(o_addr + (r + 1) * 64, o2[(r + 1) & 1][0]);
+              ptx::tmem_ld32(o_addr + (r + 1) * 64 + 32, o2[(r + 1) & 1][1]);
             }
-            // this box is free once the store BEFORE the previous one has finished reading it (DH / 32 is even: the boxes
-            // alternate across items as well); the issuing lane knows
-            if (lane == 0) ptx::tma_store_wait_read<1>();
-            __syncwarp();
-            if (ev_on) CRAM_EV(s, it, c, 14);
+            if (ev_on) CRAM_EV(s, it, r, 13);
+            uint4 v[8];
 #pragma unroll
-            for (int i = 0; i < 4; ++i)  // 64B swizzle: 16-byte chunk index ^= (row >> 1) & 3
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(box_row + ((i ^ ((lane >> 1) & 3)) << 4)), "r"(v[i].x),
+            for (int i = 0; i < 8; ++i) {
+              const uint32_t(&o)[32] = o2[r & 1][i >> 2];
+              const int k = (i & 3) * 8;
+              v[i].x = pack2<T>(__uint_as_float(o[k + 0]) * inv, __uint_as_float(o[k + 1]) * inv);
+              v[i].y = pack2<T>(__uint_as_float(o[k + 2]) * inv, __uint_as_float(o[k + 3]) * inv);
+              v[i].z = pack2<T>(__uint_as_float(o[k + 4]) * inv, __uint_as_float(o[k + 5]) * inv);
+              v[i].w = pack2<T>(__uint_as_float(o[k + 6]) * inv, __uint_as_float(o[k + 7]) * inv);
+            }
+            // the box is free once the previous store has finished READING it (the issuing lane knows)
+            if (lane == 0) ptx::tma_store_wait_read<0>();
+            __syncwarp();
+            if (ev_on) CRAM_EV(s, it, r, 14);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)  // 128B swizzle: 16-byte chunk index ^= row & 7
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(box_row + ((i ^ (lane & 7)) << 4)), "r"(v[i].x),
                            "r"(v[i].y), "r"(v[i].z), "r"(v[i].w)
                            : "memory");
             ptx::fence_proxy_async();
             __syncwarp();
             if (lane == 0) {
-              ptx::tma_store_2d(&tmap_o, box, w.head * DH + c * 32, w.q0 + slice_row0);
+              ptx::tma_store_2d(&tmap_o, box, w.head * DH + r * 64, w.q0 + slice_row0);
               ptx::tma_store_commit();
             }
           }
@@ -1064,9 +1070,7 @@ int launch_t(const cram_attn_prefill_params& p, cudaStream_t stream) {
   if ((rc = make_tmap(&tq, p.q, p.dtype, (int64_t)p.n_heads * DH, p.total_q, p.q_row_stride, kBlockM)) != CRAM_OK) return rc;
   if ((rc = make_tmap(&tk, p.k, p.dtype, (int64_t)p.n_kv_heads * DH, p.total_k, p.k_row_stride, kBlockN)) != CRAM_OK) return rc;
   if ((rc = make_tmap(&tv, p.v, p.dtype, (int64_t)p.n_kv_heads * DH, p.total_k, p.v_row_stride, kBlockN)) != CRAM_OK) return rc;
-  if ((rc = make_tmap(&to, p.out, p.dtype, (int64_t)p.n_heads * DH, p.total_q, p.out_row_stride, 32, 32,
-                      CU_TENSOR_MAP_SWIZZLE_64B)) != CRAM_OK)
-    return rc;
+  if ((rc = make_tmap(&to, p.out, p.dtype, (int64_t)p.n_heads * DH, p.total_q, p.out_row_stride, 32)) != CRAM_OK) return rc;
   const int num_pairs = (p.max_seqlen_q + kStages * kBlockM - 1) / (kStages * kBlockM);
   const long long n_items = (long long)num_pairs * p.n_seq * p.n_heads;
   if (n_items == 0) return CRAM_OK;
