@@ -269,6 +269,7 @@ __device__ __forceinline__ void score_chunk(const uint32_t (&raw)[32], const uin
     const uint64_t t23 = ffma2(pk2(__uint_as_float(raw[i + 2]), __uint_as_float(raw[i + 3])), sc2, by);
     upk2(t01, t[i + 0], t[i + 1]);
     upk2(t23, t[i + 2], t[i + 3]);
+#ifndef CRAM_ABL_NODIAG  // timing ablation: no causal predicate on diagonal tiles (wrong results on purpose)
     if (kDiag) {
       const int col = c * 32 + i;
       t[i + 0] = (col + 0 <= climit) ? t[i + 0] : -INFINITY;
@@ -276,6 +277,7 @@ __device__ __forceinline__ void score_chunk(const uint32_t (&raw)[32], const uin
       t[i + 2] = (col + 2 <= climit) ? t[i + 2] : -INFINITY;
       t[i + 3] = (col + 3 <= climit) ? t[i + 3] : -INFINITY;
     }
+#endif
   }
 }
 
@@ -336,8 +338,9 @@ __device__ __noinline__ float exact_pass(const uint32_t s_addr, const uint32_t b
 }
 
 // O *= f, l *= f (f = 2^(m_old - m_new) per row): the correction step of the online softmax
+// (l goes in and comes back by value: taken by reference it lived in local memory, in the hot loop too)
 template <int DH>
-__device__ __noinline__ void rescale_o(const uint32_t o_addr, const float f, float& l) {
+__device__ __noinline__ float rescale_o(const uint32_t o_addr, const float f, const float l) {
   const uint64_t f2 = pk2(f, f);
 #pragma unroll 1
   for (int c = 0; c < DH / 32; ++c) {
@@ -353,7 +356,7 @@ __device__ __noinline__ void rescale_o(const uint32_t o_addr, const float f, flo
     }
     ptx::tmem_st32(o_addr + c * 32, o);
   }
-  l *= f;
+  return l * f;
 }
 
 // One speculative pass over the 64 keys of half h (chunks 2h, 2h+1): P packed into pk, returns the row sum.
@@ -856,11 +859,12 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     };
 
     CRAM_EV_DECL;
-    const bool ev_on = (warp & 3) == 0 && lane == 0;
+    const bool ev_on = ((warp & 3) == 0 || (warp & 3) == 3) && lane == 0;  // rows 0-31 and 96-127 of the stage's tile
+    const int ev_slot = s + ((warp & 3) == 3 ? 4 : 0);
     for (int it = 0;; ++it) {
       const Item w = next_item(it);
       if (w.idx >= n_items) break;
-      if (ev_on) CRAM_EV(s, it, w.nt[s], 8);
+      if (ev_on) CRAM_EV(ev_slot, it, w.nt[s], 8);
       const int mt = w.pair * kStages + s;
       const int qrow = mt * kBlockM + row;          // row inside the sequence
       const int nt = w.nt[s];
@@ -873,7 +877,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         ptx::mbar_wait(&bar->bias_full[bs], (g / kBiasRing) & 1);
         ptx::mbar_wait(&bar->s_full[s], tc & 1);
         ptx::tc_fence_after();
-        if (ev_on) CRAM_EV(s, it, vt, 9);
+        if (ev_on) CRAM_EV(ev_slot, it, vt, 9);
         const bool diag_tile = p.causal && (j * kBlockN + kBlockN - 1 > mt * kBlockM + w.diag);
         const int climit = qrow + w.diag - j * kBlockN;  // columns <= climit are visible
         const uint32_t b_addr = bias_addr + bs * kBlockN * 4;
@@ -890,11 +894,14 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             // observed and Q K^T(j) was issued behind P V(j-1), so O holds every product up to tile j-1.
             const bool pend = m_next > m_ref;
             if (__any_sync(0xffffffffu, pend)) {
-              rescale_o<DH>(o_addr, pend ? ex2(m_ref - m_next) : 1.0f, l);
+              l = rescale_o<DH>(o_addr, pend ? ex2(m_ref - m_next) : 1.0f, l);
               m_ref = m_next;
             }
           }
-#pragma unroll
+          // (the diagonal instantiation runs once per item and is cold in the instruction cache every time: its two halves
+          // share one copy of the code)
+          constexpr int kUnrollH = kDiag ? 1 : 2;
+#pragma unroll kUnrollH
           for (int h = 0; h < 2; ++h) {
             uint32_t pk[32];
             const float sum = spec_half<T, kDiag>(s_base, b_addr, sc2, climit, m_ref, h, pk, [&] {
@@ -910,7 +917,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                 ptx::mbar_wait(&bar->o_half[s], tc & 1);
                 ptx::tc_fence_after();
               }
-              if (vt > 0 || h == 1) rescale_o<DH>(o_addr, (m_new > m_ref) ? ex2(m_ref - m_new) : 1.0f, l);
+              if (vt > 0 || h == 1) l = rescale_o<DH>(o_addr, (m_new > m_ref) ? ex2(m_ref - m_new) : 1.0f, l);
               m_ref = m_new;
               m_next = fmaxf(m_next, m_ref);
               l += exact_pass<T, kDiag>(s_base, b_addr, sc2, climit, m_ref, 2 * h, 2 * h + 2);
@@ -919,12 +926,13 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
               l += sum;
               if (!(sum < kSoftAbove)) m_next = fmaxf(m_next, m_ref + __log2f(sum));  // >= the true max of this half
             }
+            if (ev_on) CRAM_EV(ev_slot, it, vt, 15 - h);  // 15: half 0 done, 14: half 1 done (before its hand-over)
             if (h == 1) release(1);
           }
         };
         if (diag_tile) tile(std::true_type{});
         else tile(std::false_type{});
-        if (ev_on) CRAM_EV(s, it, vt, 10);
+        if (ev_on) CRAM_EV(ev_slot, it, vt, 10);
       }
       gt += w.n_max;
 
@@ -935,7 +943,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         ptx::mbar_wait(&bar->o_final[s], ic & 1);  // committed after the last P V of this stage and item
         ++ic;
         ptx::tc_fence_after();
-        if (ev_on) CRAM_EV(s, it, 0, 11);
+        if (ev_on) CRAM_EV(ev_slot, it, 0, 11);
         const float inv = l > 0.f ? 1.0f / l : 0.f;
         // Full 32-row slices (every warp except at the ragged end of a sequence) leave through shared memory and a TMA
         // store: one thread per row writing 16 bytes at a time straight to global memory is 32 separate 128-byte lines
@@ -959,7 +967,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
               ptx::tmem_ld32(o_addr + (r + 1) * 64, o2[(r + 1) & 1][0]);
               ptx::tmem_ld32(o_addr + (r + 1) * 64 + 32, o2[(r + 1) & 1][1]);
             }
-            if (ev_on) CRAM_EV(s, it, r, 13);
+            if (ev_on) CRAM_EV(ev_slot, it, r, 13);
             uint4 v[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -973,7 +981,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             // the box is free once the previous store has finished READING it (the issuing lane knows)
             if (lane == 0) ptx::tma_store_wait_read<0>();
             __syncwarp();
-            if (ev_on) CRAM_EV(s, it, r, 14);
+            if (ev_on) CRAM_EV(ev_slot, it, r, 14);
 #pragma unroll
             for (int i = 0; i < 8; ++i)  // 128B swizzle: 16-byte chunk index ^= row & 7
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(box_row + ((i ^ (lane & 7)) << 4)), "r"(v[i].x),
@@ -1012,7 +1020,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         for (int c = 0; c < DH; c += 8) *reinterpret_cast<uint4*>(out + c) = make_uint4(0, 0, 0, 0);
         if (p.lse) p.lse[(int64_t)w.head * p.total_q + w.q0 + qrow] = -INFINITY;
       }
-      if (ev_on) CRAM_EV(s, it, 0, 12);
+      if (ev_on) CRAM_EV(ev_slot, it, 0, 12);
     }
   }
 

@@ -3,6 +3,8 @@
 // how many cycles per element does the mix cost when the pipes are free, and do MUFU and the FMA pipe overlap?
 //   nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o softmax_mix softmax_mix.cu && ./softmax_mix
 #include <cstdio>
+#include <cstdlib>
+#include <cmath>
 #include <cuda_runtime.h>
 #include <stdint.h>
 __device__ __forceinline__ uint64_t pk2(float lo, float hi) { uint64_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
@@ -219,6 +221,13 @@ int main() {
   float* in; cudaMalloc(&in, 4096); 
   float h[1024]; for (int i = 0; i < 1024; ++i) h[i] = (i % 37) * 0.1f - 1.7f;
   cudaMemcpy(in, h, 4096, cudaMemcpyHostToDevice);
+  if (getenv("MIX_NEG_INF")) {  // every score -inf (masked keys): does MUFU.EX2 / the FP32 pipe slow down on infinities?
+    for (int i = 0; i < 1024; ++i) h[i] = (i < 128) ? 0.0f : -INFINITY;
+    cudaMemcpy(in, h, 4096, cudaMemcpyHostToDevice);
+    run<0>("full mix, all inputs -inf", in);
+    run_pipe<2, 2>(in);
+    return 0;
+  }
   float* mr; cudaMalloc(&mr, 8); cudaMemset(mr, 0, 8);
   check_poly<<<1, 1024>>>(mr);
   float hm[2]; cudaMemcpy(hm, mr, 8, cudaMemcpyDeviceToHost);

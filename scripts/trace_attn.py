@@ -32,8 +32,9 @@ def run():
     q, k, v = qkv[:, :H * dh], qkv[:, H * dh:(H + Hkv) * dh], qkv[:, (H + Hkv) * dh:]
     cu = torch.zeros(B + 1, dtype=torch.int32); cu[1:] = torch.tensor(lens).cumsum(0); cu = cu.to(dev)
     lc = torch.zeros(total, device=dev).bfloat16(); lc[100:900] = -0.69
+    causal = os.environ.get("TRACE_CAUSAL", "1") != "0"
     for _ in range(3):
-        ops.attn_prefill(q, k, v, cu, T, H, Hkv, dh, logcred=lc, head_mask=0x0FFFFFFF, kernel=2)
+        ops.attn_prefill(q, k, v, cu, T, H, Hkv, dh, logcred=lc, head_mask=0x0FFFFFFF, kernel=2, causal=causal)
     torch.cuda.synchronize()
     lib = _lib.load()
     buf = np.zeros((24, 64, 4), dtype=np.int64)
@@ -61,11 +62,11 @@ def run():
         names = {0: "P take.start", 1: "P published next", 2: "P first loads issued", 3: "P all loads issued", 4: "M s0 PV+QK issued",
                  5: "M s1 PV+QK issued", 6: "M next item read", 7: "M next first QK issued", 8: "S item read", 9: "S S(j) seen",
                  10: "S tile done", 11: "S o_final seen", 12: "S epilogue done", 13: "S epilogue: O chunk in registers",
-                 14: "S epilogue: box free"}
-        role = {0: "softmax0", 1: "softmax1", 2: "mma", 3: "producer"}
+                 14: "S half 1 done / epilogue: box free", 15: "S half 0 done"}
+        role = {0: "softmax0", 1: "softmax1", 2: "mma", 3: "producer", 4: "softmax0.w3", 5: "softmax1.w3"}
         lo, hi = (int(x) for x in os.environ.get("TRACE_ITEMS", "6,9").split(","))
         rows = []
-        for slot in range(4):
+        for slot in range(6):
             for n in range(2048):
                 c, tag = int(ev[slot, n, 0]), int(ev[slot, n, 1])
                 if c == 0:
