@@ -952,31 +952,33 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         // the copy engine does the rest while the warp goes on. (Boxes of 32 columns, double-buffered, measured the same.)
         const int slice_row0 = mt * kBlockM + (warp & 3) * 32;
         if (slice_row0 + 32 <= w.len_q) {
-          // rounds of 64 columns: one 4 KB box per warp (32 rows x 128 bytes, 128B swizzle), one TMA store per round; the
-          // TMEM loads of the next round are in flight while this one is scaled, packed and staged
+          // rounds of 64 columns: one 4 KB box per warp (32 rows x 128 bytes, 128B swizzle), one TMA store per round
           uint8_t* box = smem + S::kOut + warp * 2 * S::kOutBoxBytes;
           const uint32_t box_row = ptx::smem_u32(box) + lane * 128;
-          uint32_t o2[2][2][32];
-          ptx::tmem_ld32(o_addr, o2[0][0]);
-          ptx::tmem_ld32(o_addr + 32, o2[0][1]);
-#pragma unroll
+          const uint64_t inv2 = pk2(inv, inv);
+          // (not unrolled, packed multiplies: this code runs once per item and is cold in the instruction cache -- its size
+          // costs more than the TMEM latency a prefetch across rounds would hide)
+#pragma unroll 1
           for (int r = 0; r < DH / 64; ++r) {
-            ptx::tc_wait_ld_regs(o2[r & 1][0]);
-            ptx::tc_wait_ld_regs(o2[r & 1][1]);
-            if (r + 1 < DH / 64) {
-              ptx::tmem_ld32(o_addr + (r + 1) * 64, o2[(r + 1) & 1][0]);
-              ptx::tmem_ld32(o_addr + (r + 1) * 64 + 32, o2[(r + 1) & 1][1]);
-            }
+            uint32_t oa[32], ob[32];
+            ptx::tmem_ld32(o_addr + r * 64, oa);
+            ptx::tmem_ld32(o_addr + r * 64 + 32, ob);
+            ptx::tc_wait_ld_regs(oa);
+            ptx::tc_wait_ld_regs(ob);
             if (ev_on) CRAM_EV(ev_slot, it, r, 13);
             uint4 v[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-              const uint32_t(&o)[32] = o2[r & 1][i >> 2];
+              const uint32_t(&o)[32] = i < 4 ? oa : ob;
               const int k = (i & 3) * 8;
-              v[i].x = pack2<T>(__uint_as_float(o[k + 0]) * inv, __uint_as_float(o[k + 1]) * inv);
-              v[i].y = pack2<T>(__uint_as_float(o[k + 2]) * inv, __uint_as_float(o[k + 3]) * inv);
-              v[i].z = pack2<T>(__uint_as_float(o[k + 4]) * inv, __uint_as_float(o[k + 5]) * inv);
-              v[i].w = pack2<T>(__uint_as_float(o[k + 6]) * inv, __uint_as_float(o[k + 7]) * inv);
+              float f[8];
+#pragma unroll
+              for (int e = 0; e < 8; e += 2)
+                upk2(fmul2(pk2(__uint_as_float(o[k + e]), __uint_as_float(o[k + e + 1])), inv2), f[e], f[e + 1]);
+              v[i].x = pack2<T>(f[0], f[1]);
+              v[i].y = pack2<T>(f[2], f[3]);
+              v[i].z = pack2<T>(f[4], f[5]);
+              v[i].w = pack2<T>(f[6], f[7]);
             }
             // the box is free once the previous store has finished READING it (the issuing lane knows)
             if (lane == 0) ptx::tma_store_wait_read<0>();
