@@ -1,4 +1,4 @@
-// Kernel (1): fused credibility-biased FlashAttention-style prefill for sm_100a (v5: two query tiles
+// Kernel (1): fused credibility-biased FlashAttention-style prefill for sm_100a (v5.22: persistent, two query tiles
 // per CTA, ping-pong softmax warpgroups, 128-key tiles).
 //
 //   S = Q K^T      tcgen05.mma (SS) M128 x N128 x K16, 128x128 fp32 accumulator in TMEM, operands TMA-staged in
@@ -28,8 +28,15 @@
 // alternate on the tensor pipe: while warpgroup s runs the softmax of tile j, the MMA warp runs
 // P V (j) and Q K^T (j+1) of the other stage. TMEM: S0 | S1 | O0 | O1 (4 x 128 columns); P (64 packed columns)
 // aliases the first half of S, so per stage the chain is softmax(j) -> P V(j) -> Q K^T(j+1) -> softmax(j+1).
-// Lazy O rescale (only when a row's max grows by more than 2^8) keeps the correction off the hot loop, and lets the
-// exponentials of a tile be issued speculatively against the standing reference max, in the pass that forms the scores.
+// There is no running max in the hot loop: the exponentials of a half-tile are taken against a standing reference, its row
+// sum is the overflow detector, the reference moves lazily and one tile late (see the softmax section below).
+//
+// PERSISTENT: one CTA per SM walks a dynamic queue of work items (256 rows of one sequence and head); the next item is
+// taken three tiles before the end of the current one. On heads that carry the bias, 128-key tiles whose keys all have
+// credibility 0 are never visited (live_tiles_kernel + LiveTiles). The output leaves through shared memory and TMA stores.
+// The kernel is instruction-cache sensitive: code that runs once per item (the diagonal tile's body, the epilogue, the
+// rare exact path) is kept small or out of line -- profiles/r2_attn_ablation_and_trace.md has the event logs behind each
+// of these choices.
 #include <atomic>
 #include <cstdlib>
 #include <mutex>
@@ -53,7 +60,6 @@ constexpr int kSched = 4;           // scheduler ring depth (work items publishe
 constexpr int kItemConsumers = 10;  // MMA warp, bias warp, eight softmax warps (lane 0 of each frees a slot)
 constexpr int kTmemCols = 512;
 constexpr float kLog2e = 1.4426950408889634f;
-constexpr float kRescaleThreshold = 8.0f;  // log2 units
 // Debug timeline (scripts/trace_attn.py builds a separate library with -DCRAM_ATTN_TRACE=<block>; the product
 // build compiles none of this): clock64 stamps of one CTA's softmax warps, MMA issuer and producer, per tile.
 #ifdef CRAM_ATTN_TRACE
