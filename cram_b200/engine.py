@@ -322,12 +322,13 @@ class CramEngine:
         return self.logits(x)
 
     @torch.no_grad()
-    def prefill_into_cache(self, prompts: Sequence[torch.Tensor], kv: PagedKV, block_table: torch.Tensor,
+    def prefill_into_cache(self, prompts: Sequence[torch.Tensor], kv: Optional[PagedKV], block_table: Optional[torch.Tensor],
                            logcreds: Optional[Sequence[torch.Tensor]] = None,
                            head_masks: Optional[Sequence[int]] = None, chunk: int = 16) -> torch.Tensor:
         """Re-weighted prefill of a batch of prompts (each a 1-D int64 CUDA tensor) into the paged cache,
-        `chunk` sequences per pass (bounds the activation footprint). Returns last-row logits [B, vocab]."""
-        dev, ps = self.device, kv.page_size
+        `chunk` sequences per pass (bounds the activation footprint). Returns last-row logits [B, vocab].
+        ``kv`` None: no decode step follows (max_new_tokens <= 1), nothing is cached."""
+        dev, ps = self.device, (kv.page_size if kv is not None else 1)
         out = []
         for b0 in range(0, len(prompts), chunk):
             part = list(prompts[b0:b0 + chunk])
@@ -337,9 +338,11 @@ class CramEngine:
             cu_d = cu.to(dev)
             ids = torch.cat(part).to(dev)
             positions = packed_positions(cu_d, ids.numel())
-            seq_of_row = torch.repeat_interleave(torch.arange(b0, b0 + len(part), device=dev), torch.tensor(lens, device=dev))
-            pos64 = positions.to(torch.int64)
-            slot = block_table[seq_of_row, pos64 // ps].to(torch.int64) * ps + pos64 % ps
+            slot = None
+            if kv is not None:
+                seq_of_row = torch.repeat_interleave(torch.arange(b0, b0 + len(part), device=dev), torch.tensor(lens, device=dev))
+                pos64 = positions.to(torch.int64)
+                slot = block_table[seq_of_row, pos64 // ps].to(torch.int64) * ps + pos64 % ps
             lc = torch.cat(list(logcreds[b0:b0 + chunk])).to(dev) if logcreds is not None else None
             x = self.prefill(ids, cu_d, max(lens), logcred=lc, head_masks=head_masks, kv=kv, slot_mapping=slot,
                              positions=positions)
@@ -367,8 +370,10 @@ class CramEngine:
         lens = [int(p.numel()) for p in prompts]
         max_total = max(lens) + max_new_tokens
         pages_per_seq = (max_total + page_size - 1) // page_size
-        kv = PagedKV(s, B * pages_per_seq, page_size, self.dtype, dev)
-        block_table = torch.arange(B * pages_per_seq, dtype=torch.int32, device=dev).view(B, pages_per_seq)
+        kv = block_table = None
+        if max_new_tokens > 1:  # a single new token comes straight from the prefill's last-row logits: no cache, no decode
+            kv = PagedKV(s, B * pages_per_seq, page_size, self.dtype, dev)
+            block_table = torch.arange(B * pages_per_seq, dtype=torch.int32, device=dev).view(B, pages_per_seq)
         logits = self.prefill_into_cache(prompts, kv, block_table, logcreds, head_masks)
         # decode-time bias: [B, T0max] padded with zeros, keys < bias_len[b] biased
         lc_dec = bias_len = None
