@@ -304,3 +304,49 @@ def test_sm100_dead_tiles_long_sequences_and_mask_layout_limits():
     got = ops.attn_prefill(q[:total], k[:total], v[:total], cu[:1025], max(lens), H, Hkv, dh, logcred=lc[:total], head_mask=0b11,
                            kernel=SM100)
     assert report("1024 prompts: masks", got, want[:total]) <= 2e-2
+
+
+@pytest.mark.parametrize("seed", list(range(12)))
+def test_sm100_randomized_configurations(seed):
+    """Seeded random draw over everything the entry point takes at once: ragged batches, GQA ratio, head dim, dtype, causal or
+    not, chunked prefill (len_q < len_k) with or without bias_len, head masks with high bits, dead spans that may or may
+    not cover whole tiles, an output buffer with a row stride of its own -- tcgen05 kernel vs the fp64 statement of the
+    contract, and vs the CUDA-core kernel."""
+    rng = np.random.default_rng(1000 + seed)
+    dh = int(rng.choice([64, 128]))
+    Hkv = int(rng.choice([1, 2, 4, 8]))
+    H = Hkv * int(rng.choice([1, 2, 4, 7, 8]))
+    dtype = torch.bfloat16 if rng.random() < 0.7 else torch.float16
+    causal = bool(rng.random() < 0.8)
+    n_seq = int(rng.integers(1, 7))
+    lens_k = [int(x) for x in rng.integers(1, 1400, size=n_seq)]
+    chunked = bool(rng.random() < 0.4)
+    lens_q = [int(rng.integers(1, lk + 1)) for lk in lens_k] if chunked else list(lens_k)
+    q, _, _, _ = make_qkv(sum(lens_q), H, Hkv, dh, dtype, DEV, seed=2000 + seed)
+    _, k, v, _ = make_qkv(sum(lens_k), H, Hkv, dh, dtype, DEV, seed=3000 + seed)
+    lc = make_logcred(lens_k, DEV, dtype, seed=4000 + seed)
+    for s_ in range(n_seq):  # dead spans of random extent
+        if rng.random() < 0.6 and lens_k[s_] > 10:
+            a = int(rng.integers(0, lens_k[s_] - 1))
+            b = int(rng.integers(a + 1, min(lens_k[s_], a + 700) + 1))
+            off = sum(lens_k[:s_])
+            lc[off + a:off + b] = float("-inf")
+    mask = int(rng.integers(1, 1 << min(H, 62))) | (1 << (H - 1))
+    bl = None
+    if chunked and rng.random() < 0.5:
+        bl = torch.tensor([int(rng.integers(0, lk + 1)) for lk in lens_k], dtype=torch.int32, device=DEV)
+    cuq, cuk = cu_of(lens_q, DEV), cu_of(lens_k, DEV)
+    pad = 8 * int(rng.integers(0, 3))
+    buf = torch.full((sum(lens_q), H * dh + pad), float("nan"), dtype=dtype, device=DEV)
+    out = buf[:, :H * dh]
+    kw = dict(logcred=lc, head_mask=mask, cu_seqlens_k=cuk, max_seqlen_k=max(lens_k), bias_len=bl, causal=causal)
+    got = ops.attn_prefill(q, k, v, cuq, max(lens_q), H, Hkv, dh, kernel=SM100, out=out, **kw)
+    want = ref_attention(q, k, v, cuq, cuk, H, Hkv, dh, logcred=lc, head_mask=mask,
+                         bias_len=None if bl is None else bl.tolist(), causal=causal)
+    desc = f"random {seed}: H={H}/{Hkv} dh={dh} {dtype} causal={causal} chunked={chunked} lens_k={lens_k}"
+    assert not torch.isnan(got).any(), desc
+    assert report(desc, got, want) <= 2e-2
+    if pad:
+        assert torch.isnan(buf[:, H * dh:]).all(), "wrote outside the output columns"
+    gen = ops.attn_prefill(q, k, v, cuq, max(lens_q), H, Hkv, dh, kernel=GENERIC, **kw)
+    assert report(desc + " vs generic", got, gen.double()) <= 2e-2
