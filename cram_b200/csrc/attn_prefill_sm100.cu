@@ -653,7 +653,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
           // first loads). Taking costs ~3800 cycles of dependent global latency (a contended atomic, cu_seqlens, the mask
           // word); there the producer is between two ring-slot waits with a tile of slack, while at the top of the loop
           // (v5.4) it sat in front of the next item's Q / K[0] at every item boundary (event log:
-          // profiles/r2_attn_evlog.md). It is also the latest point that still has the next item's record and first
+          // profiles/r2_attn_ablation_and_trace.md). It is also the latest point that still has the next item's record and first
           // loads out before the consumers get there -- and the later an item is claimed from the dynamic queue, the
           // better the balance at the tail (claiming one more item ahead cost 7 % at 16 x 2048 causal).
           Item w_next;
