@@ -587,7 +587,7 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
   };
 
   if (warp >= 8) {
-    setmaxnreg_dec<56>();
+    setmaxnreg_dec<104>();
     if (warp == 8) {
       // ============================== scheduler + producer =======================================
       // Per item: K[0], Q of both stages (once the previous item's last Q K^T of that stage has completed), K[1], then per
@@ -846,7 +846,10 @@ attn_prefill_sm100_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     // softmax warps
   } else {
     // ============================== softmax / correction / epilogue ================================
-    setmaxnreg_inc<224>();
+    // 200 / 104 registers (softmax / the other four warps): 256 x (200 - 168) = 128 x (168 - 104). The softmax code does not
+    // spill at 192; at 224 / 56 the producer's work items lived in local memory, and 200 / 104 measured 0.5-1 % faster
+    // (profiles/ab_regs.txt).
+    setmaxnreg_inc<200>();
     const int s = warp >> 2;                      // query stage of this warpgroup
     const int row = (warp & 3) * 32 + lane;       // row inside the tile == TMEM lane
     const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
