@@ -99,7 +99,12 @@ class CramEngine:
         # decode steps of <= 64 sequences run the MLP through cram_linear_decode (CRAM_B200_STREAMING_MLP=0: library GEMMs)
         self.streaming_mlp = os.environ.get("CRAM_B200_STREAMING_MLP", "1") != "0"
         # the two small projections (qkv, o_proj) as well; off by default: the library GEMM is faster at 25-33 MB
-        self.streaming_proj = os.environ.get("CRAM_B200_STREAMING_PROJ", "0") != "0"
+        # decode step: qkv / o_proj through cram_linear_decode instead of the library GEMM (off by default: measured slower
+        # in the step, profiles/r2_decode_streaming_proj_ab.txt). "1" = both, "qkv" / "o" = one of them (A/B runs).
+        _sp = os.environ.get("CRAM_B200_STREAMING_PROJ", "0")
+        self.streaming_proj = _sp != "0"
+        self.streaming_qkv = _sp in ("1", "qkv")
+        self.streaming_o = _sp in ("1", "o")
         if os.environ.get("CRAM_B200_PDL"):  # A/B timing only: 0 switches programmatic dependent launch off
             ops._lib.load().cram_debug_pdl(int(os.environ["CRAM_B200_PDL"]))
         if os.environ.get("CRAM_B200_LINEAR_RING"):  # A/B timing only: force the 4- or 8-stage ring everywhere
@@ -181,7 +186,7 @@ class CramEngine:
         rows also go to their cache slots in the same launch as the rotation."""
         s = self.spec
         h = ops.rmsnorm(x, self.w[f"in_norm.{l}"], s.rms_eps, residual=pending)  # x += pending (in place)
-        if self.streaming_proj and kv is not None and h.shape[0] <= 64 and h.dtype in (torch.bfloat16, torch.float16):
+        if self.streaming_qkv and kv is not None and h.shape[0] <= 64 and h.dtype in (torch.bfloat16, torch.float16):
             qkv = ops.linear_decode(h, self.w[f"wqkv.{l}"], self.w.get(f"bqkv.{l}"))
         else:
             qkv = F.linear(h, self.w[f"wqkv.{l}"], self.w.get(f"bqkv.{l}"))
@@ -202,7 +207,7 @@ class CramEngine:
         the delta is already in x (``streaming_mlp``: the <= 64-row decode step, where gate/up + SwiGLU and
         down + residual add each run as one weight-streaming launch of cram_linear_decode)."""
         s = self.spec
-        if streaming_mlp and self.streaming_proj:
+        if streaming_mlp and self.streaming_o:
             ops.linear_decode(attn, self.w[f"wo.{l}"], mode=ops.LINEAR_RESIDUAL, out=x)
             h = ops.rmsnorm(x, self.w[f"post_norm.{l}"], s.rms_eps)
         else:
