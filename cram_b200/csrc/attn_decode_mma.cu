@@ -11,6 +11,8 @@
 //     t = S*scale*log2e + (head selected ? logcred[key]*log2e : 0)
 // Legacy mma.sync is deliberate here: the contraction is 16 x 64 x 128 per tile and the kernel is
 // bound by the cache stream, not by the tensor pipe.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace cram {
@@ -375,6 +377,11 @@ bool attn_decode_mma_supported(const cram_attn_decode_params& p) {
 
 // splits: fill the resident CTA slots (2 per SM) once; never fewer than the page table staging allows
 int attn_decode_mma_splits(const cram_attn_decode_params& p) {
+  static const int forced = [] {  // A/B runs only: CRAM_B200_DECODE_SPLITS=<n> overrides the choice below
+    const char* e = getenv("CRAM_B200_DECODE_SPLITS");
+    return e ? atoi(e) : 0;
+  }();
+  if (forced > 0) return forced;
   const int base = p.n_seq * p.n_kv_heads;
   int want = (2 * sm_count()) / (base > 0 ? base : 1);
   const int max_by_len = (p.max_seqlen + 4 * kTileKeys - 1) / (4 * kTileKeys);  // >= 256 keys per split
